@@ -1,0 +1,31 @@
+# Builds the C-ABI library of the B200 primary-ray path: librt_b200.so (sm_100a only, no CPU fallback).
+PKG   := triangles_sdf_cpu_raytracing_b200
+CSRC  := $(PKG)/csrc
+NVCC  ?= /usr/local/cuda/bin/nvcc
+ARCH  := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall
+OUT   := $(PKG)/librt_b200.so
+OBJ   := $(CSRC)/build
+
+$(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o
+	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart shared
+
+$(OBJ)/rt_kernels_exact.o: $(CSRC)/rt_kernels_exact.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
+
+$(OBJ)/rt_kernels_fast.o: $(CSRC)/rt_kernels_fast.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -fmad=true -c $< -o $@
+
+$(OBJ)/rt_api.o: $(CSRC)/rt_api.cu $(CSRC)/rt_scene.h $(CSRC)/bvh_builder.h include/rt_b200.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(OBJ)/bvh_builder.o: $(CSRC)/bvh_builder.cpp $(CSRC)/bvh_builder.h $(CSRC)/rt_scene.h include/rt_b200.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+.PHONY: clean
+clean:
+	rm -rf $(OBJ) $(OUT)

@@ -1,0 +1,158 @@
+/* rt_b200.h — C ABI of the B200 (sm_100a) primary-ray hot path.
+ *
+ * This is the drop-in boundary for ONE path of iMacsimus/Triangles-SDF-CPU-RayTracing: everything that
+ * happens between `Renderer::draw(scene, frameBuffer, camera, projInv)` (src/raytracing.cpp:67-102) and
+ * the framebuffer writes, for the three scene types (triangles_raytracing.cpp, grid_raytracing.cpp,
+ * octree_raytracing.cpp) plus the ISPC primitives they call (ray_pack.ispc).  All `file:line` citations are
+ * into the reference tree.  Plain pointers and sizes only; no C++ / torch types; no exceptions cross it.
+ *
+ * Conventions
+ *   - every entry point returns RT_OK (0) or a negative rt_status; rt_last_error() gives the text
+ *     (the reference has no error reporting on this path);
+ *   - matrices are 16 floats, column-major, i.e. the memory image of LiteMath::float4x4::m_col
+ *     (external/LiteMath/LiteMath.h:1396-1462);
+ *   - framebuffers are row-major, index row*W + x with memory row 0 = TOP of the image, exactly
+ *     FrameBuffer::color / FrameBuffer::t (src/raytracing.hpp:9-20, Image2d.h:91);
+ *   - the depth buffer is IN/OUT: a pixel is overwritten only by a hit closer than the value it holds
+ *     (raytracing.cpp:17,90-94); "cleared" means colour 0 and t = +inf (raytracing.hpp:16-19);
+ *   - a scene lives on the CUDA device that was current when it was created; it is immutable afterwards
+ *     and may be rendered from any host thread.
+ *   - there is NO CPU fallback: without a CUDA device every call fails with RT_ERR_CUDA.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum rt_status {
+  RT_OK = 0,
+  RT_ERR_INVALID = -1, /* bad argument / malformed scene data (e.g. octree child offset out of range) */
+  RT_ERR_CUDA = -2,    /* CUDA runtime failure, including "no device" */
+  RT_ERR_UNSUPPORTED = -3
+} rt_status;
+
+/* ShadingMode, src/raytracing.hpp:99 (same order). */
+typedef enum rt_shading_mode { RT_SHADE_NORMAL = 0, RT_SHADE_LAMBERT = 1, RT_SHADE_COLOR = 2 } rt_shading_mode;
+
+/* Arithmetic flavour of the kernels.
+ * RT_MATH_EXACT: every FP32 operation is issued separately, in the reference's operator order (no FMA
+ *   contraction), IEEE div/sqrt: bit-identical to the reference built with -ffp-contract=off.
+ * RT_MATH_FAST : same algorithm, the compiler may contract a*b+c into FMA (what GCC/ISPC do by default
+ *   in the reference's Release build). */
+typedef enum rt_math_mode { RT_MATH_EXACT = 0, RT_MATH_FAST = 1 } rt_math_mode;
+
+/* Ray-to-thread scheduling of the render kernels.
+ * RT_SCHED_TILES     : one thread per pixel, 8x4-pixel warp tiles, one launch covers the frame.
+ * RT_SCHED_PERSISTENT: persistent warps pull 8x4 tiles from an atomic counter and refill retired lanes
+ *   (ballot compaction) so early-terminating rays do not idle a warp.
+ * RT_SCHED_AUTO      : the per-scene-type default chosen by measurement. */
+typedef enum rt_sched_mode { RT_SCHED_AUTO = 0, RT_SCHED_TILES = 1, RT_SCHED_PERSISTENT = 2 } rt_sched_mode;
+
+/* Dense-grid storage in HBM. LINEAR = the on-disk order (x-major, z fastest, grid_raytracing.hpp:13-15);
+ * BRICKS = 8x8x8-sample bricks so the 8 corners of a trilinear cell share few 128-byte lines. */
+typedef enum rt_grid_layout { RT_GRID_AUTO = 0, RT_GRID_LINEAR = 1, RT_GRID_BRICKS = 2 } rt_grid_layout;
+
+/* Triangle-scene traversal. BVH8 = our 8-wide BVH; BRUTE = every ray tests every triangle from shared
+ * memory (the loop ray_pack.ispc:167-202 describes; only for small meshes). */
+typedef enum rt_mesh_accel { RT_MESH_AUTO = 0, RT_MESH_BVH8 = 1, RT_MESH_BRUTE = 2 } rt_mesh_accel;
+
+typedef enum rt_scene_kind { RT_SCENE_GRID = 0, RT_SCENE_OCTREE = 1, RT_SCENE_MESH = 2 } rt_scene_kind;
+
+#define RT_PRIM_MISS 0xFFFFFFFFu  /* prim id of a pixel that was not written */
+#define RT_PRIM_PLANE 0xFFFFFFFEu /* the checkerboard ground plane (src/raytracing.hpp:119-186) */
+
+typedef struct rt_scene rt_scene; /* opaque */
+
+/* Everything Renderer::draw derives per frame (raytracing.cpp:73-75) plus the Renderer's public knobs
+ * (raytracing.hpp:103-106) and the part of the frame this call renders. */
+typedef struct rt_frame {
+  float ray_pos[3];   /* camera.position() */
+  float view_inv[16]; /* inverse4x4(camera.lookAtMatrix()) */
+  float proj_inv[16]; /* the projInv argument of draw */
+  uint32_t width, height; /* full frame */
+  /* Screen-space partition (multi-GPU tiles): this call renders the memory rows r with
+   * (r / band_rows) % band_count == band_index.  {0,0,0} or band_count <= 1 means the whole frame. */
+  uint32_t band_rows, band_count, band_index;
+  int32_t shading_mode;     /* rt_shading_mode */
+  float light_pos[3];       /* Renderer::lightPos (main.cpp:60: {2,2,2}) */
+  int32_t enable_shadows;   /* Renderer::enableShadows   (secondary rays) */
+  int32_t enable_reflections; /* Renderer::enableReflections (only the plane reflects) */
+  int32_t has_plane;        /* SceneUnion(model, Plane({0,1,0}, plane_y)), main.cpp:189-190 */
+  float plane_y;
+  float t_near, t_far;      /* raytracing.cpp:90 passes 0.01, 100; 0,0 selects those defaults */
+} rt_frame;
+
+/* per-frame workload counters (filled when requested; sums over all rays of the call) */
+typedef struct rt_counters {
+  uint64_t rays, hits;
+  uint64_t grid_samples;                       /* SDFGrid::sdf(float3) evaluations */
+  uint64_t oct_inner, oct_leaf, oct_leaf_samples;
+  uint64_t bvh_inner, bvh_leaf, bvh_tris;
+} rt_counters;
+
+/* ---- library / device ------------------------------------------------------------------------- */
+const char *rt_last_error(void);         /* thread-local text of the last failure */
+const char *rt_version(void);
+int rt_device_count(int *count);         /* number of visible CUDA devices */
+int rt_set_device(int device);           /* cudaSetDevice for the calling thread */
+
+/* ---- scene construction (upload once) ---------------------------------------------------------- */
+/* replaces SDFGrid + loadSDFGrid (grid_raytracing.hpp:10-22, .cpp:127-134): values[(x*sy + y)*sz + z] */
+int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t sz, int layout /*rt_grid_layout*/,
+                         rt_scene **out);
+/* replaces SDFOctree + loadSDFOctree (octree_raytracing.hpp:8-49, .cpp:8-16): n x 36-byte
+ * {float values[8]; uint32 childrenOffset}.  Offsets and depth are validated (a bad offset would be an
+ * out-of-bounds device read). */
+int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out);
+/* replaces BVHBuilder::perform (triangles_raytracing.hpp:40, .cpp:227-258): builds our own 8-wide BVH on the
+ * host and uploads it with the leaf triangles pre-gathered.  vpos4 = SimpleMesh::vPos4f (x,y,z,w),
+ * indices = SimpleMesh::indices (3 per triangle); prim id = triangle index in this order. */
+int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices,
+                         int accel /*rt_mesh_accel*/, rt_scene **out);
+/* same, but traverses a BVH8 the reference's own BVHBuilder produced: nodes = n_nodes x node_bytes (204)
+ * images of BVH8Node (triangles_raytracing.hpp:10-36), indices in the builder's permuted order, and
+ * prim_of_permuted[i] = original id of permuted triangle i (NULL: identity). */
+int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices_bvh, uint32_t n_indices,
+                              const void *nodes, uint32_t n_nodes, uint32_t node_bytes,
+                              const uint32_t *prim_of_permuted, rt_scene **out);
+void rt_scene_destroy(rt_scene *scene);
+int rt_scene_kind_of(const rt_scene *scene);             /* rt_scene_kind */
+int rt_scene_device(const rt_scene *scene);
+/* bytes of scene data resident in HBM, and the model's bounding box (meshes: calc_bbox, raytracing.hpp:22-37;
+ * SDF scenes: [-1,1]^3) */
+int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]);
+
+/* ---- options (process-wide defaults; reads are racy by design, set them before rendering) ------- */
+int rt_set_math_mode(int mode /*rt_math_mode*/);
+int rt_set_sched_mode(int mode /*rt_sched_mode*/);
+
+/* ---- rendering: replaces the body of Renderer::draw (raytracing.cpp:67-102) ---------------------- */
+/* Device-resident framebuffer, asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default
+ * stream).  color/t/prim are device pointers to W*H elements (they may be peer-mapped memory of another
+ * GPU: the kernel then stores its tiles straight into the root framebuffer over NVLink).  t_in may equal
+ * t_out (the reference's in/out depth buffer) or be NULL (= cleared, +inf).  prim and counters may be NULL;
+ * counters is a DEVICE pointer to an rt_counters that is accumulated into. */
+int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *color, const float *t_in, float *t_out,
+                     uint32_t *prim, rt_counters *counters_dev, void *stream);
+/* Host framebuffer, synchronous, exactly the reference's call: copies t in, renders, copies colour / t
+ * (/ prim) out.  Returns the device time of the render kernels alone in *device_ms (the reference returns
+ * its own stopwatch, raytracing.cpp:97-101) and of the whole call incl. copies in *total_ms.  Any of prim,
+ * device_ms, total_ms, counters may be NULL. */
+int rt_render_host(const rt_scene *scene, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
+                   float *device_ms, float *total_ms, rt_counters *counters);
+
+/* ---- single rays: replaces IScene::intersect (raytracing.hpp:75-81) for n rays at once ------------ */
+/* origins/dirs: n x 3 floats (host).  Outputs (host, n elements; normal n x 3; any may be NULL):
+ * hit (0/1), t, the unflipped HitInfo::normal, prim id. */
+int rt_intersect_host(const rt_scene *scene, const float *origins, const float *dirs, uint32_t n, float t_near,
+                      float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
+                      uint32_t *prim);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

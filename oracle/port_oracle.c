@@ -452,9 +452,30 @@ static BvhHit bvh_node(const PortScene *s, uint32_t index, v3 o, v3 d, float tNe
   return result;
 }
 
+/* No BVH given: every triangle in index order, first closest wins (the loop ray_pack.ispc:167-202 describes,
+ * with the leaf acceptance rule of triangles_raytracing.cpp:324-331: no t-range test). Tree-independent truth
+ * for meshes whose reference-built BVH is not at hand (the GPU box). nIdx is passed in nBvhNodes' place. */
+static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, PortCounters *cnt) {
+  BvhHit result = {0, INFINITY, 0};
+  uint32_t nTri = s->bvhNodeBytes; /* triangle count when bvhNodes == NULL */
+  for (uint32_t k = 0; k < nTri; ++k) {
+    if (cnt) cnt->bvhTris++;
+    v3 v0 = mesh_vertex(s, s->indices[3 * k]);
+    v3 v1 = mesh_vertex(s, s->indices[3 * k + 1]);
+    v3 v2 = mesh_vertex(s, s->indices[3 * k + 2]);
+    float th;
+    if (tri_lane(o, d, v0, v1, v2, &th) && (!result.hitten || result.t > th)) {
+      result.hitten = 1;
+      result.t = th;
+      result.tri = k;
+    }
+  }
+  return result;
+}
+
 static Hit mesh_intersect(const PortScene *s, v3 o, v3 d, float tNear, float tFar, PortCounters *cnt) {
   Hit r = hit_none();
-  BvhHit b = bvh_node(s, 0, o, d, tNear, tFar, cnt);
+  BvhHit b = s->bvhNodes ? bvh_node(s, 0, o, d, tNear, tFar, cnt) : mesh_brute(s, o, d, cnt);
   if (!b.hitten) return r;
   r.hitten = 1;
   r.t = b.t;

@@ -139,6 +139,21 @@ class Scene:
             s.c.primOfPermuted = p.ctypes.data
         return s
 
+    @staticmethod
+    def mesh_brute(vpos4, indices) -> "Scene":
+        """Mesh without a BVH: every ray tests every triangle in index order (tree-independent closest hit)."""
+        s = Scene()
+        v = np.ascontiguousarray(vpos4, np.float32).reshape(-1, 4)
+        i = np.ascontiguousarray(indices, np.uint32).reshape(-1)
+        s._keep += [v, i]
+        s.c.kind = 2
+        s.c.vpos4 = v.ctypes.data
+        s.c.indices = i.ctypes.data
+        s.c.bvhNodes = None
+        s.c.nBvhNodes = 0
+        s.c.bvhNodeBytes = i.size // 3  # triangle count (see port_oracle.c mesh_brute)
+        return s
+
     def with_plane(self, y: float) -> "Scene":
         s = Scene()
         C.memmove(C.byref(s.c), C.byref(self.c), C.sizeof(PortScene))

@@ -1,0 +1,53 @@
+"""CPU: the C-ABI library loads and exports every symbol include/rt_b200.h declares; without a GPU every compute
+entry point fails loudly (there is no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import triangles_sdf_cpu_raytracing_b200 as rt
+from triangles_sdf_cpu_raytracing_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = rt.lib()
+    names = _declared()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/rt_b200.h but not exported"
+    assert set(names) == set(_lib.SIGNATURES), "ctypes signature table out of sync with the header"
+
+
+def test_struct_layouts_match_header():
+    # rt_frame: 3+16+16 floats, 5 u32, i32, 3 floats, 3 i32, 1 float, 2 floats
+    assert C.sizeof(rt.RtFrame) == 4 * (3 + 16 + 16 + 5 + 1 + 3 + 3 + 1 + 2)
+    assert C.sizeof(rt.RtCounters) == 9 * 8
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(rt.RtError):
+        rt.SDFGrid(np.zeros((4, 4, 4), np.float32))
+
+
+def test_argument_validation_reports_errors():
+    lib = rt.lib()
+    h = C.c_void_p()
+    assert lib.rt_scene_create_grid(None, 4, 4, 4, 0, C.byref(h)) == -1
+    assert b"null" in lib.rt_last_error()
+    assert lib.rt_scene_create_octree(None, 0, C.byref(h)) == -1
+    assert lib.rt_set_math_mode(7) == -1
+    assert lib.rt_set_sched_mode(-1) == -1
+    assert lib.rt_scene_kind_of(None) == -1

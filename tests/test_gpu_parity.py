@@ -1,0 +1,183 @@
+"""GPU: the CUDA path, called through the C ABI, against (a) the golden frames the reference itself rendered and
+(b) the plain-C oracle on the same seeded inputs.  RT_MATH_EXACT must be bit-identical; RT_MATH_FAST must meet the
+north-star tolerances (hit mask exact bar counted pixels, depth 1e-4 relative, RGB within 1/255)."""
+import numpy as np
+import pytest
+
+import triangles_sdf_cpu_raytracing_b200 as rt
+from oracle import port_oracle as P
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+G = util.Golden()
+SDF_CASES = [c for c in G.cases if c.split("|")[0] in ("example_grid", "sdf_5", "sdf_6")]
+MESH_CASES = [c for c in G.cases if c.split("|")[0] in util.MESHES]
+_scene_cache = {}
+
+
+def scene(name, **kw):
+    key = (name, tuple(sorted(kw.items())))
+    if key not in _scene_cache:
+        _scene_cache[key] = util.cuda_scene(G, name, **kw)
+    return _scene_cache[key]
+
+
+@pytest.fixture(autouse=True)
+def _defaults():
+    rt.set_math_mode(rt.MATH_EXACT)
+    rt.set_sched_mode(rt.SCHED_AUTO)
+    yield
+    rt.set_math_mode(rt.MATH_EXACT)
+    rt.set_sched_mode(rt.SCHED_AUTO)
+
+
+def _frame(c, **kw):
+    return rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"], **kw)
+
+
+@pytest.mark.parametrize("sched", (rt.SCHED_TILES, rt.SCHED_PERSISTENT))
+@pytest.mark.parametrize("key", SDF_CASES)
+def test_sdf_scenes_bit_exact_vs_reference(key, sched):
+    rt.set_sched_mode(sched)
+    c = G.case(key)
+    s = scene(c["scene"])
+    for mode, name in ((rt.SHADE_NORMAL, "color_normal"), (rt.SHADE_LAMBERT, "color_lambert"),
+                       (rt.SHADE_COLOR, "color_color")):
+        r = s.render(_frame(c, mode=mode))
+        assert util.same_bits(r["t"], c["t"]), f"{key}: depth differs on {(util.bits(r['t']) != util.bits(c['t'])).sum()} px"
+        assert np.array_equal(r["color"], c[name]), f"{key}: {name} differs"
+    # in/out depth buffer
+    t0 = np.full((c["H"], c["W"]), 2.2, np.float32)
+    c0 = np.full((c["H"], c["W"]), 0x11223344, np.uint32)
+    r = s.render(_frame(c), color=c0, t=t0)
+    assert util.same_bits(r["t"], c["t_prefilled"]) and np.array_equal(r["color"], c["color_prefilled"])
+
+
+def test_grid_brick_layout_is_bit_exact():
+    for key in [c for c in SDF_CASES if c.startswith("example_grid")]:
+        c = G.case(key)
+        r = scene("example_grid", layout=rt.GRID_BRICKS).render(_frame(c))
+        assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
+
+
+@pytest.mark.parametrize("accel", (rt.MESH_BVH8, rt.MESH_BRUTE))
+@pytest.mark.parametrize("key", MESH_CASES)
+def test_mesh_scenes_vs_reference(key, accel):
+    c = G.case(key)
+    if accel == rt.MESH_BRUTE and c["scene"] != "cube":
+        pytest.skip("brute force is for small meshes")
+    s = scene(c["scene"], accel=accel)
+    r = s.render(_frame(c), want_prim=True)
+    # closest hit does not depend on the tree: depth and colour are bit-identical, prim ids may differ on exact ties
+    assert util.same_bits(r["t"], c["t"]), f"{key}: depth differs on {(util.bits(r['t']) != util.bits(c['t'])).sum()} px"
+    assert np.array_equal(r["color"], c["color_normal"])
+    ties = r["prim"] != c["prim"]
+    assert ties.sum() <= max(2, 0.002 * ties.size), f"{key}: {ties.sum()} prim-id mismatches"
+    r = s.render(_frame(c, mode=rt.SHADE_LAMBERT))
+    assert np.array_equal(r["color"], c["color_lambert"])
+
+
+def test_reference_built_bvh_is_traversed_identically():
+    a = G.scene_arrays("cube_refbvh")
+    s = rt.TriangleMeshFromReferenceBVH(a["vpos4"], a["indices_bvh"], a["nodes"], a["prim_of_permuted"])
+    for key in [c for c in MESH_CASES if c.startswith("cube|")]:
+        c = G.case(key)
+        r = s.render(_frame(c), want_prim=True)
+        assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
+        assert np.array_equal(r["prim"], c["prim"])
+        # with the reference's own tree even the tree-dependent tFar quirk is reproduced
+        t0 = np.full((c["H"], c["W"]), 2.2, np.float32)
+        c0 = np.full((c["H"], c["W"]), 0x11223344, np.uint32)
+        r = s.render(_frame(c), color=c0, t=t0)
+        assert util.same_bits(r["t"], c["t_prefilled"]) and np.array_equal(r["color"], c["color_prefilled"])
+
+
+@pytest.mark.parametrize("name", ("example_grid", "sdf_6", "stanford-bunny", "cube"))
+def test_single_rays_match_reference(name):
+    """IScene::intersect on seeded rays incl. exactly axis-parallel ones (inf / NaN slab arithmetic)."""
+    k = G.kats
+    hit, t, n, _ = scene(name).intersect(k[f"ray_{name}_o"], k[f"ray_{name}_d"])
+    want = k[f"ray_{name}_hit"].astype(bool)
+    assert np.array_equal(hit, want)
+    assert util.same_bits(t[want], k[f"ray_{name}_t"][want])
+    assert util.same_bits(n[want], k[f"ray_{name}_n"][want])
+
+
+@pytest.mark.parametrize("name,W,H", (("example_grid", 480, 270), ("sdf_6", 480, 270), ("stanford-bunny", 320, 180),
+                                      ("cube", 256, 256)))
+def test_larger_frames_vs_c_oracle(name, W, H):
+    """Same seeded inputs through the plain-C oracle at a size it finishes in seconds; counters must agree too."""
+    c = G.case([k for k in G.cases if k.startswith(name + "|default")][0])
+    # the projection only depends on the aspect ratio: reuse the golden camera when it matches
+    assert abs(W / H - c["W"] / c["H"]) < 1e-6
+    ps = util.port_scene(G, name)
+    want_c, want_t, want_p, want_cnt = ps.render(c["rayPos"], c["viewInv"], c["projInv"], W, H, want_counters=True)
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+    r = scene(name).render(f, want_prim=True, want_counters=True)
+    assert util.same_bits(r["t"], want_t) and np.array_equal(r["color"], want_c)
+    if name in ("example_grid", "sdf_6"):
+        assert np.array_equal(r["prim"], want_p)
+        cn = r["counters"]
+        assert cn["rays"] == want_cnt["rays"] and cn["hits"] == want_cnt["hits"]
+        assert cn["grid_samples"] == want_cnt["gridSdf"]
+        assert cn["oct_inner"] == want_cnt["octInner"] and cn["oct_leaf"] == want_cnt["octLeaf"]
+        assert cn["oct_leaf_samples"] == want_cnt["octLeafSdf"]
+    else:
+        assert (r["prim"] != want_p).sum() <= max(2, 0.002 * W * H)
+
+
+@pytest.mark.parametrize("key", [c for c in G.cases if "|default|" in c or "|orbit5|" in c])
+def test_fast_math_meets_north_star_tolerances(key):
+    rt.set_math_mode(rt.MATH_FAST)
+    c = G.case(key)
+    r = scene(c["scene"]).render(_frame(c))
+    d = util.compare_frames(r["color"], r["t"], c["color_normal"], c["t"])
+    n = c["W"] * c["H"]
+    # grazing / edge pixels are counted and bounded, not hidden
+    assert d["mask_mismatch"] <= 0.002 * n, d
+    assert d["depth_outliers"] <= 0.005 * n, d
+    assert d["rgb_outliers"] <= 0.005 * n, d
+
+
+def test_screen_space_bands_compose_the_full_frame():
+    """Multi-GPU partition (interleaved row bands): the union of all bands equals the single-call frame."""
+    c = G.case("sdf_6|default|160x90")
+    s = scene("sdf_6")
+    full = s.render(_frame(c))
+    for band_rows, count in ((8, 2), (16, 4), (7, 3), (32, 8)):
+        color = np.zeros((c["H"], c["W"]), np.uint32)
+        t = np.full((c["H"], c["W"]), np.inf, np.float32)
+        for i in range(count):
+            r = s.render(_frame(c, bands=(band_rows, count, i)), color=color, t=t)
+            color, t = r["color"], r["t"]
+        assert util.same_bits(t, full["t"]) and np.array_equal(color, full["color"])
+
+
+def test_edge_cases():
+    # 1x1 and ragged sizes (not multiples of the 8x4 warp tile)
+    c = G.case("example_grid|default|160x90")
+    s = scene("example_grid")
+    ps = util.port_scene(G, "example_grid")
+    for W, H in ((1, 1), (3, 5), (33, 9), (8, 4)):
+        pinv = c["projInv"]  # aspect differs: still a valid projection, both sides get the same matrix
+        wc, wt, _, _ = ps.render(c["rayPos"], c["viewInv"], pinv, W, H)
+        r = s.render(rt.make_frame(c["rayPos"], c["viewInv"], pinv, W, H))
+        assert util.same_bits(r["t"], wt) and np.array_equal(r["color"], wc)
+    # degenerate scenes
+    one = np.zeros((1, 36), np.uint8)  # a single all-zero leaf: isEmpty
+    r = rt.SDFOctree(one).render(_frame(c))
+    assert not np.isfinite(r["t"]).any()
+    with pytest.raises(rt.RtError):
+        bad = np.zeros((2, 36), np.uint8)
+        bad[0, 32:36] = np.array([5], np.uint32).view(np.uint8)  # children 5..12 out of range
+        rt.SDFOctree(bad)
+    with pytest.raises(rt.RtError):
+        rt.TriangleMesh(np.zeros((3, 4), np.float32), np.array([0, 1, 7], np.uint32))
+    with pytest.raises(rt.RtError):
+        rt.SDFGrid(np.zeros((1, 4, 4), np.float32))
+    # a degenerate triangle never hits (|det| < 1e-8) and does not poison its neighbours
+    v = np.array([[0, 0, 0, 1], [1, 0, 0, 1], [2, 0, 0, 1], [-1, -1, 0, 1], [1, -1, 0, 1], [0, 1, 0, 1]], np.float32)
+    m = rt.TriangleMesh(v, np.array([0, 1, 2, 3, 4, 5], np.uint32))
+    hit, t, n, prim = m.intersect(np.array([[0, 0, 2.5]], np.float32), np.array([[0, 0, -1]], np.float32))
+    assert hit[0] and prim[0] == 1 and t[0] == np.float32(2.5)

@@ -1,0 +1,94 @@
+"""CPU: the plain-C oracle (oracle/port_oracle.c) against the committed golden vectors that the reference's own
+unmodified C++ produced (tests/golden/make_golden.py), bit for bit. This is what pins the oracle."""
+import numpy as np
+import pytest
+
+from oracle import port_oracle as P
+from tests import util
+
+
+def _cases(kind=None):
+    g = util.Golden()
+    return [c for c in g.cases if kind is None or c.split("|")[0] in kind]
+
+
+@pytest.mark.parametrize("key", _cases())
+def test_port_frame_matches_reference_bit_for_bit(golden, key):
+    c = golden.case(key)
+    s = util.port_scene(golden, c["scene"])
+    for mode, name in ((P.MODE_NORMAL, "color_normal"), (P.MODE_LAMBERT, "color_lambert"), (P.MODE_COLOR, "color_color")):
+        col, t, prim, _ = s.render(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"], mode=mode)
+        assert util.same_bits(t, c["t"]), f"{key}: depth differs"
+        assert np.array_equal(col, c[name]), f"{key}: {name} differs"
+    if c["prim"] is not None:
+        # brute force keeps the lowest prim id on exact ties; the reference keeps its BVH's first: allow tie pixels
+        diff = prim != c["prim"]
+        assert diff.mean() < 0.01, f"{key}: prim ids differ on {diff.sum()} pixels"
+
+
+@pytest.mark.parametrize("key", _cases(("cube", "example_grid", "sdf_6")))
+def test_port_prefilled_depth_buffer(golden, key):
+    """the framebuffer is in/out; only closer hits overwrite."""
+    c = golden.case(key)
+    if c["scene"] == "cube":
+        # Triangle hits are not range-checked: with tFar = tPrev a hit behind tPrev is still accepted
+        # when its leaf box starts before tPrev, so the outcome depends on the tree: use the reference's own.
+        a = golden.scene_arrays("cube_refbvh")
+        s = P.Scene.mesh(a["vpos4"], a["indices_bvh"], a["nodes"], a["prim_of_permuted"])
+    else:
+        s = util.port_scene(golden, c["scene"])
+    t0 = np.full((c["H"], c["W"]), 2.2, np.float32)
+    c0 = np.full((c["H"], c["W"]), 0x11223344, np.uint32)
+    col, t, _, _ = s.render(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"], color=c0, t=t0)
+    assert util.same_bits(t, c["t_prefilled"])
+    assert np.array_equal(col, c["color_prefilled"])
+
+
+def test_port_reference_bvh_traversal(golden):
+    """The port's BVH8 traversal over the reference-built tree (cube) gives the reference's prim ids exactly."""
+    a = golden.scene_arrays("cube_refbvh")
+    s = P.Scene.mesh(a["vpos4"], a["indices_bvh"], a["nodes"], a["prim_of_permuted"])
+    for key in _cases(("cube",)):
+        c = golden.case(key)
+        col, t, prim, _ = s.render(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"])
+        assert util.same_bits(t, c["t"]) and np.array_equal(col, c["color_normal"])
+        assert np.array_equal(prim, c["prim"])
+
+
+def test_port_kats(golden):
+    k = golden.kats
+    for i in range(k["slab_boxes"].shape[0]):
+        got = P.intersect_box_8(k["slab_boxes"][i], k["slab_org"][i], k["slab_inv"][i], 0.01, 100.0)
+        assert util.same_bits(got, k["slab_t"][i])
+        t1, t2, face = P.bbox_intersection(k["slab_boxes"][i, :3, 0], k["slab_boxes"][i, 3:, 0], k["slab_org"][i],
+                                           k["slab_inv"][i], 0.01, 100.0)
+        assert util.same_bits(t1, k["bbox_t1"][i]) and util.same_bits(t2, k["bbox_t2"][i]) and face == k["bbox_face"][i]
+        st, si = P.sort8(k["sort_in"][i])
+        assert util.same_bits(st, k["sort_t"][i]) and np.array_equal(si, k["sort_idx"][i])
+        for lane in range(8):
+            hit, t, n = P.triangle(k["tri_o"][i], k["tri_d"][i], k["tri_v"][i, lane])
+            assert hit == bool(k["tri_hit"][i, lane])
+            if hit:
+                assert util.same_bits(t, k["tri_t"][i, lane]) and util.same_bits(n, k["tri_n"][i, lane])
+    g = util.port_scene(golden, "example_grid")
+    for p, sd, nrm in zip(k["grid_p"], k["grid_sdf"], k["grid_normal"]):
+        assert util.same_bits(g.grid_sdf(p), sd)
+        assert util.same_bits(g.grid_normal(p), nrm)
+    for (x, y), d in zip(k["eye_xy"], k["eye_dir"]):
+        got = P.eye_ray(np.zeros(3, np.float32), k["eye_viewInv"], k["eye_projInv"], 96, 64, int(x), int(y))
+        assert util.same_bits(got, d)
+    for c, want in zip(k["pack_in"], k["pack_out"]):
+        assert P.color_pack(c) == int(want)
+
+
+@pytest.mark.parametrize("name", ("example_grid", "sdf_6", "stanford-bunny", "cube"))
+def test_port_single_rays(golden, name):
+    k = golden.kats
+    s = util.port_scene(golden, name)
+    o, d = k[f"ray_{name}_o"], k[f"ray_{name}_d"]
+    for i in range(o.shape[0]):
+        hit, t, n, _ = s.intersect(o[i], d[i])
+        assert hit == bool(k[f"ray_{name}_hit"][i]), f"ray {i}"
+        if hit:
+            assert util.same_bits(t, k[f"ray_{name}_t"][i]), f"ray {i}"
+            assert util.same_bits(n, k[f"ray_{name}_n"][i]), f"ray {i}"

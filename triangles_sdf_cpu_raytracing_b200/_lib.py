@@ -1,0 +1,90 @@
+"""ctypes binding of librt_b200.so (include/rt_b200.h). There is no fallback: a missing library is an error."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+
+RT_OK = 0
+SHADE_NORMAL, SHADE_LAMBERT, SHADE_COLOR = 0, 1, 2
+MATH_EXACT, MATH_FAST = 0, 1
+SCHED_AUTO, SCHED_TILES, SCHED_PERSISTENT = 0, 1, 2
+GRID_AUTO, GRID_LINEAR, GRID_BRICKS = 0, 1, 2
+MESH_AUTO, MESH_BVH8, MESH_BRUTE = 0, 1, 2
+SCENE_GRID, SCENE_OCTREE, SCENE_MESH = 0, 1, 2
+PRIM_MISS = 0xFFFFFFFF
+PRIM_PLANE = 0xFFFFFFFE
+
+
+class RtFrame(C.Structure):
+    _fields_ = [
+        ("ray_pos", C.c_float * 3), ("view_inv", C.c_float * 16), ("proj_inv", C.c_float * 16),
+        ("width", C.c_uint32), ("height", C.c_uint32),
+        ("band_rows", C.c_uint32), ("band_count", C.c_uint32), ("band_index", C.c_uint32),
+        ("shading_mode", C.c_int32), ("light_pos", C.c_float * 3),
+        ("enable_shadows", C.c_int32), ("enable_reflections", C.c_int32),
+        ("has_plane", C.c_int32), ("plane_y", C.c_float),
+        ("t_near", C.c_float), ("t_far", C.c_float),
+    ]
+
+
+class RtCounters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays", "hits", "grid_samples", "oct_inner", "oct_leaf",
+                                          "oct_leaf_samples", "bvh_inner", "bvh_leaf", "bvh_tris")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+# every symbol include/rt_b200.h declares: name -> (restype, argtypes)
+_vp, _u32, _i, _f = C.c_void_p, C.c_uint32, C.c_int, C.c_float
+_pp = C.POINTER(C.c_void_p)
+SIGNATURES = {
+    "rt_last_error": (C.c_char_p, []),
+    "rt_version": (C.c_char_p, []),
+    "rt_device_count": (_i, [C.POINTER(_i)]),
+    "rt_set_device": (_i, [_i]),
+    "rt_scene_create_grid": (_i, [_vp, _u32, _u32, _u32, _i, _pp]),
+    "rt_scene_create_octree": (_i, [_vp, _u32, _pp]),
+    "rt_scene_create_mesh": (_i, [_vp, _u32, _vp, _u32, _i, _pp]),
+    "rt_scene_create_mesh_bvh8": (_i, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _vp, _pp]),
+    "rt_scene_destroy": (None, [_vp]),
+    "rt_scene_kind_of": (_i, [_vp]),
+    "rt_scene_device": (_i, [_vp]),
+    "rt_scene_info": (_i, [_vp, C.POINTER(C.c_uint64), C.POINTER(_f), C.POINTER(_f)]),
+    "rt_set_math_mode": (_i, [_i]),
+    "rt_set_sched_mode": (_i, [_i]),
+    "rt_render_device": (_i, [_vp, C.POINTER(RtFrame), _vp, _vp, _vp, _vp, _vp, _vp]),
+    "rt_render_host": (_i, [_vp, C.POINTER(RtFrame), _vp, _vp, _vp, C.POINTER(_f), C.POINTER(_f),
+                            C.POINTER(RtCounters)]),
+    "rt_intersect_host": (_i, [_vp, _vp, _vp, _u32, _f, _f, _i, _f, _vp, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+class RtError(RuntimeError):
+    pass
+
+
+def lib() -> C.CDLL:
+    """Loads the CUDA library. Raises if it has not been built (`make` or __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RtError(f"{LIB_PATH} is missing: build it with `make` at the repository root "
+                          "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int):
+    if rc != RT_OK:
+        raise RtError(f"rt_b200 error {rc}: {lib().rt_last_error().decode()}")

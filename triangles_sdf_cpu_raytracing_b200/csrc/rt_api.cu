@@ -1,0 +1,506 @@
+// extern "C" boundary of the B200 primary-ray path (include/rt_b200.h): scene upload, validation, launches.
+// No CPU fallback lives here: every entry point needs a CUDA device.
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "bvh_builder.h"
+#include "rt_scene.h"
+
+using namespace rt;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<int> g_math{RT_MATH_EXACT};
+std::atomic<int> g_sched{RT_SCHED_AUTO};
+
+int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+int cuda_fail(cudaError_t e, const char *what) {
+  g_err = std::string(what) + ": " + cudaGetErrorString(e);
+  return RT_ERR_CUDA;
+}
+#define RT_CUDA(call)                                  \
+  do {                                                 \
+    cudaError_t e__ = (call);                          \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+constexpr int N_TILE_COUNTERS = 64;
+
+}  // namespace
+
+struct rt_scene {
+  int kind = -1;
+  int device = 0;
+  int sm_count = 148;
+  SceneDev dev{};
+  std::vector<void *> allocs;
+  uint64_t bytes = 0;
+  float bbox_min[3] = {-1, -1, -1}, bbox_max[3] = {1, 1, 1};
+  uint32_t *tile_counters = nullptr;  // ring, one per in-flight persistent launch
+  std::atomic<uint32_t> next_counter{0};
+  // framebuffer cache of rt_render_host
+  std::mutex host_mu;
+  uint32_t *h_color = nullptr;
+  float *h_t = nullptr;
+  uint32_t *h_prim = nullptr;
+  rt_counters *h_cnt = nullptr;
+  size_t h_pixels = 0;
+  cudaStream_t h_stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+namespace {
+
+int scene_begin(rt_scene **out, rt_scene *&s) {
+  if (!out) return fail(RT_ERR_INVALID, "out pointer is null");
+  *out = nullptr;
+  int dev = 0;
+  RT_CUDA(cudaGetDevice(&dev));
+  s = new rt_scene;
+  s->device = dev;
+  cudaDeviceProp p;
+  cudaError_t e = cudaGetDeviceProperties(&p, dev);
+  if (e != cudaSuccess) {
+    delete s;
+    return cuda_fail(e, "cudaGetDeviceProperties");
+  }
+  s->sm_count = p.multiProcessorCount;
+  return RT_OK;
+}
+
+template <class T>
+int upload(rt_scene *s, const T *host, size_t n, const T **devOut) {
+  void *d = nullptr;
+  size_t bytes = std::max<size_t>(n * sizeof(T), 16);
+  RT_CUDA(cudaMalloc(&d, bytes));
+  s->allocs.push_back(d);
+  s->bytes += n * sizeof(T);
+  if (n) RT_CUDA(cudaMemcpy(d, host, n * sizeof(T), cudaMemcpyHostToDevice));
+  *devOut = static_cast<const T *>(d);
+  return RT_OK;
+}
+
+int scene_finish(rt_scene *s, rt_scene **out) {
+  void *d = nullptr;
+  RT_CUDA(cudaMalloc(&d, N_TILE_COUNTERS * sizeof(uint32_t)));
+  s->allocs.push_back(d);
+  s->tile_counters = static_cast<uint32_t *>(d);
+  RT_CUDA(cudaMemset(d, 0, N_TILE_COUNTERS * sizeof(uint32_t)));
+  RT_CUDA(cudaDeviceSynchronize());
+  *out = s;
+  return RT_OK;
+}
+
+void scene_free(rt_scene *s) {
+  if (!s) return;
+  DeviceGuard g(s->device);
+  for (void *p : s->allocs) cudaFree(p);
+  if (s->h_color) cudaFree(s->h_color);
+  if (s->h_t) cudaFree(s->h_t);
+  if (s->h_prim) cudaFree(s->h_prim);
+  if (s->h_cnt) cudaFree(s->h_cnt);
+  for (auto &e : s->ev)
+    if (e) cudaEventDestroy(e);
+  if (s->h_stream) cudaStreamDestroy(s->h_stream);
+  delete s;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *rt_last_error(void) { return g_err.c_str(); }
+const char *rt_version(void) { return "rt_b200 0.1 (sm_100a)"; }
+
+int rt_device_count(int *count) {
+  if (!count) return fail(RT_ERR_INVALID, "count is null");
+  *count = 0;
+  RT_CUDA(cudaGetDeviceCount(count));
+  return RT_OK;
+}
+
+int rt_set_device(int device) {
+  RT_CUDA(cudaSetDevice(device));
+  return RT_OK;
+}
+
+int rt_set_math_mode(int mode) {
+  if (mode != RT_MATH_EXACT && mode != RT_MATH_FAST) return fail(RT_ERR_INVALID, "unknown math mode");
+  g_math = mode;
+  return RT_OK;
+}
+
+int rt_set_sched_mode(int mode) {
+  if (mode < RT_SCHED_AUTO || mode > RT_SCHED_PERSISTENT) return fail(RT_ERR_INVALID, "unknown sched mode");
+  g_sched = mode;
+  return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- grid
+int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t sz, int layout, rt_scene **out) {
+  if (!values) return fail(RT_ERR_INVALID, "grid values pointer is null");
+  // SDFGrid::sdf maps [-1,1] to [0,size-1] (grid_raytracing.cpp:8-11): every axis needs two samples
+  if (sx < 2 || sy < 2 || sz < 2) return fail(RT_ERR_INVALID, "grid needs at least 2 samples per axis");
+  if ((uint64_t)sx * sy * sz >= (1ull << 32)) return fail(RT_ERR_INVALID, "grid too large (cell index must fit 32 bits)");
+  if (layout < RT_GRID_AUTO || layout > RT_GRID_BRICKS) return fail(RT_ERR_INVALID, "unknown grid layout");
+  rt_scene *s = nullptr;
+  int rc = scene_begin(out, s);
+  if (rc) return rc;
+  s->kind = RT_SCENE_GRID;
+  s->dev.kind = RT_SCENE_GRID;
+  GridDev &g = s->dev.grid;
+  g.sx = sx; g.sy = sy; g.sz = sz;
+  const size_t n = (size_t)sx * sy * sz;
+  if (layout == RT_GRID_AUTO) layout = RT_GRID_LINEAR;  // chosen by measurement, DESIGN.md "grid layout"
+  if (layout == RT_GRID_BRICKS) {
+    const uint32_t nbx = (sx + 7) / 8, nby = (sy + 7) / 8, nbz = (sz + 7) / 8;
+    std::vector<float> b((size_t)nbx * nby * nbz * 512, 0.0f);
+    for (uint32_t x = 0; x < sx; ++x)
+      for (uint32_t y = 0; y < sy; ++y) {
+        const float *src = values + ((size_t)x * sy + y) * sz;
+        for (uint32_t z = 0; z < sz; ++z) {
+          size_t br = ((size_t)(x >> 3) * nby + (y >> 3)) * nbz + (z >> 3);
+          b[(br << 9) + (((x & 7u) << 6) | ((y & 7u) << 3) | (z & 7u))] = src[z];
+        }
+      }
+    g.bricks = 1; g.nby = nby; g.nbz = nbz;
+    rc = upload(s, b.data(), b.size(), &g.values);
+  } else {
+    g.bricks = 0; g.nby = g.nbz = 0;
+    rc = upload(s, values, n, &g.values);
+  }
+  if (rc == RT_OK) rc = scene_finish(s, out);
+  if (rc != RT_OK) scene_free(s);
+  return rc;
+}
+
+// -------------------------------------------------------------------------------------------- octree
+int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out) {
+  if (!nodes36 || n_nodes == 0) return fail(RT_ERR_INVALID, "octree needs at least the root node");
+  const uint8_t *raw = static_cast<const uint8_t *>(nodes36);
+  std::vector<uint32_t> link(n_nodes);
+  std::vector<float> vals((size_t)n_nodes * 8);
+  for (uint32_t i = 0; i < n_nodes; ++i) {
+    std::memcpy(&vals[(size_t)i * 8], raw + (size_t)i * 36, 32);
+    std::memcpy(&link[i], raw + (size_t)i * 36 + 32, 4);
+  }
+  // validate: every inner node's 8 children in range, each node reached at most once (a tree), bounded depth
+  std::vector<uint8_t> seen(n_nodes, 0);
+  std::vector<std::pair<uint32_t, uint32_t>> stack{{0u, 0u}};
+  seen[0] = 1;
+  uint32_t depth = 0;
+  while (!stack.empty()) {
+    auto [node, lvl] = stack.back();
+    stack.pop_back();
+    depth = std::max(depth, lvl);
+    uint32_t off = link[node];
+    if (off == 0) continue;
+    if ((uint64_t)off + 7 >= n_nodes) return fail(RT_ERR_INVALID, "octree childrenOffset out of range");
+    if (lvl + 1 > (uint32_t)OCT_MAX_DEPTH) return fail(RT_ERR_INVALID, "octree deeper than the supported 22 levels");
+    for (uint32_t c = 0; c < 8; ++c) {
+      if (seen[off + c]) return fail(RT_ERR_INVALID, "octree node referenced twice (not a tree)");
+      seen[off + c] = 1;
+      stack.push_back({off + c, lvl + 1});
+    }
+  }
+  // leaf classification, from the values alone: isEmpty (octree_raytracing.hpp:12-17) or all >= 1e-4 (.cpp:132-135)
+  for (uint32_t i = 0; i < n_nodes; ++i) {
+    if (link[i] != 0) continue;
+    const float *v = &vals[(size_t)i * 8];
+    bool allBig = true, allZero = true, allPos = true;
+    for (int k = 0; k < 8; ++k) {
+      if (!(v[k] > 10.0f)) allBig = false;
+      if (!(v[k] == 0.0f)) allZero = false;
+      if (!(v[k] >= 1e-4f)) allPos = false;
+    }
+    link[i] = (allBig || allZero || allPos) ? OCT_LEAF_CULLED : OCT_LEAF_SURFACE;
+  }
+  rt_scene *s = nullptr;
+  int rc = scene_begin(out, s);
+  if (rc) return rc;
+  s->kind = RT_SCENE_OCTREE;
+  s->dev.kind = RT_SCENE_OCTREE;
+  s->dev.oct.n_nodes = n_nodes;
+  s->dev.oct.depth = depth;
+  rc = upload(s, link.data(), link.size(), &s->dev.oct.link);
+  const float *dv = nullptr;
+  if (rc == RT_OK) rc = upload(s, vals.data(), vals.size(), &dv);
+  s->dev.oct.values = reinterpret_cast<const float4 *>(dv);
+  if (rc == RT_OK) rc = scene_finish(s, out);
+  if (rc != RT_OK) scene_free(s);
+  return rc;
+}
+
+// ---------------------------------------------------------------------------------------------- mesh
+static int finish_mesh(HostBvh &h, bool brute, rt_scene **out) {
+  rt_scene *s = nullptr;
+  int rc = scene_begin(out, s);
+  if (rc) return rc;
+  s->kind = RT_SCENE_MESH;
+  s->dev.kind = RT_SCENE_MESH;
+  MeshDev &m = s->dev.mesh;
+  m.n_tris = (uint32_t)h.tris.size();
+  m.n_nodes = (uint32_t)h.nodes.size();
+  m.brute = brute ? 1u : 0u;
+  for (int a = 0; a < 3; ++a) {
+    s->bbox_min[a] = h.bbox_min[a];
+    s->bbox_max[a] = h.bbox_max[a];
+  }
+  rc = upload(s, h.tris.data(), h.tris.size(), &m.tris);
+  if (rc == RT_OK) rc = upload(s, h.nodes.data(), h.nodes.size(), &m.nodes);
+  if (rc == RT_OK) rc = scene_finish(s, out);
+  if (rc != RT_OK) scene_free(s);
+  return rc;
+}
+
+int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, int accel,
+                         rt_scene **out) {
+  if (accel < RT_MESH_AUTO || accel > RT_MESH_BRUTE) return fail(RT_ERR_INVALID, "unknown mesh accel");
+  const uint32_t nTri = n_indices / 3;
+  // brute force keeps the whole mesh in shared memory: 48 B per triangle, up to 4096 triangles (192 KB)
+  if (accel == RT_MESH_AUTO) accel = nTri <= 32 ? RT_MESH_BRUTE : RT_MESH_BVH8;
+  if (accel == RT_MESH_BRUTE && nTri > 4096) return fail(RT_ERR_UNSUPPORTED, "brute force is limited to 4096 triangles");
+  HostBvh h;
+  std::string err;
+  if (!build_bvh8(vpos4, n_verts, indices, n_indices, accel == RT_MESH_BRUTE, h, err)) return fail(RT_ERR_INVALID, err);
+  return finish_mesh(h, accel == RT_MESH_BRUTE, out);
+}
+
+int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices_bvh, uint32_t n_indices,
+                              const void *nodes, uint32_t n_nodes, uint32_t node_bytes,
+                              const uint32_t *prim_of_permuted, rt_scene **out) {
+  HostBvh h;
+  std::string err;
+  if (!import_reference_bvh(vpos4, n_verts, indices_bvh, n_indices, nodes, n_nodes, node_bytes, prim_of_permuted, h,
+                            err))
+    return fail(RT_ERR_INVALID, err);
+  return finish_mesh(h, false, out);
+}
+
+void rt_scene_destroy(rt_scene *scene) { scene_free(scene); }
+
+int rt_scene_kind_of(const rt_scene *scene) { return scene ? scene->kind : RT_ERR_INVALID; }
+int rt_scene_device(const rt_scene *scene) { return scene ? scene->device : RT_ERR_INVALID; }
+
+int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]) {
+  if (!scene) return fail(RT_ERR_INVALID, "scene is null");
+  if (device_bytes) *device_bytes = scene->bytes;
+  for (int a = 0; a < 3; ++a) {
+    if (bbox_min) bbox_min[a] = scene->bbox_min[a];
+    if (bbox_max) bbox_max[a] = scene->bbox_max[a];
+  }
+  return RT_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================================
+// rendering
+// =============================================================================================================
+namespace {
+
+int make_frame(const rt_frame *f, FrameDev &d) {
+  if (!f) return fail(RT_ERR_INVALID, "frame is null");
+  if (f->width == 0 || f->height == 0) return fail(RT_ERR_INVALID, "frame has zero size");
+  if ((uint64_t)f->width * f->height >= (1ull << 31)) return fail(RT_ERR_INVALID, "frame too large");
+  if (f->shading_mode < RT_SHADE_NORMAL || f->shading_mode > RT_SHADE_COLOR)
+    return fail(RT_ERR_INVALID, "unknown shading mode");
+  std::memcpy(d.ray_pos, f->ray_pos, sizeof d.ray_pos);
+  std::memcpy(d.view_inv, f->view_inv, sizeof d.view_inv);
+  std::memcpy(d.proj_inv, f->proj_inv, sizeof d.proj_inv);
+  d.W = f->width;
+  d.H = f->height;
+  if (f->band_count <= 1) {
+    d.band_rows = f->height;
+    d.band_count = 1;
+    d.band_index = 0;
+    d.rows_here = f->height;
+  } else {
+    if (f->band_rows == 0 || f->band_index >= f->band_count) return fail(RT_ERR_INVALID, "bad band partition");
+    d.band_rows = f->band_rows;
+    d.band_count = f->band_count;
+    d.band_index = f->band_index;
+    const uint32_t nBands = (f->height + f->band_rows - 1) / f->band_rows;
+    const uint32_t mine = nBands > f->band_index ? (nBands - f->band_index + f->band_count - 1) / f->band_count : 0;
+    d.rows_here = mine * f->band_rows;  // the last band may be short: kernels also test row < H
+  }
+  d.mode = f->shading_mode;
+  std::memcpy(d.light, f->light_pos, sizeof d.light);
+  d.shadows = f->enable_shadows != 0;
+  d.reflections = f->enable_reflections != 0;
+  d.has_plane = f->has_plane != 0;
+  d.plane_y = f->plane_y;
+  const bool defaults = f->t_near == 0.0f && f->t_far == 0.0f;
+  d.t_near = defaults ? 0.01f : f->t_near;  // raytracing.cpp:90
+  d.t_far = defaults ? 100.0f : f->t_far;
+  return RT_OK;
+}
+
+// per-scene-type default scheduling, chosen by measurement (DESIGN.md "scheduling")
+int resolve_sched(const rt_scene *s) {
+  int m = g_sched.load();
+  if (m != RT_SCHED_AUTO) return m;
+  (void)s;
+  return RT_SCHED_TILES;
+}
+
+int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color, const float *t_in, float *t_out,
+                     uint32_t *prim, rt_counters *counters_dev, cudaStream_t st) {
+  RenderArgs a;
+  a.scene = scene->dev;
+  a.frame = fd;
+  a.color = color;
+  a.t_in = t_in;
+  a.t_out = t_out;
+  a.prim = prim;
+  a.counters = reinterpret_cast<unsigned long long *>(counters_dev);
+  rt_scene *ms = const_cast<rt_scene *>(scene);
+  a.tile_counter = scene->tile_counters + (ms->next_counter.fetch_add(1) % N_TILE_COUNTERS);
+  const int sched = resolve_sched(scene);
+  cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, scene->sm_count, st)
+                                                  : exact::launch_render(a, sched, scene->sm_count, st);
+  if (e != cudaSuccess) return cuda_fail(e, "render launch");
+  return RT_OK;
+}
+
+int ensure_host_buffers(rt_scene *s, size_t pixels) {
+  if (!s->h_stream) {
+    RT_CUDA(cudaStreamCreateWithFlags(&s->h_stream, cudaStreamNonBlocking));
+    for (auto &e : s->ev) RT_CUDA(cudaEventCreate(&e));
+    RT_CUDA(cudaMalloc(&s->h_cnt, sizeof(rt_counters)));
+  }
+  if (pixels > s->h_pixels) {
+    if (s->h_color) cudaFree(s->h_color);
+    if (s->h_t) cudaFree(s->h_t);
+    if (s->h_prim) cudaFree(s->h_prim);
+    s->h_color = nullptr; s->h_t = nullptr; s->h_prim = nullptr; s->h_pixels = 0;
+    RT_CUDA(cudaMalloc(&s->h_color, pixels * 4));
+    RT_CUDA(cudaMalloc(&s->h_t, pixels * 4));
+    RT_CUDA(cudaMalloc(&s->h_prim, pixels * 4));
+    s->h_pixels = pixels;
+  }
+  return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *color, const float *t_in, float *t_out,
+                     uint32_t *prim, rt_counters *counters_dev, void *stream) {
+  if (!scene) return fail(RT_ERR_INVALID, "scene is null");
+  if (!color || !t_out) return fail(RT_ERR_INVALID, "color / t_out must not be null");
+  FrameDev fd;
+  int rc = make_frame(frame, fd);
+  if (rc) return rc;
+  DeviceGuard g(scene->device);
+  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
+  return render_on_stream(scene, fd, color, t_in, t_out, prim, counters_dev, static_cast<cudaStream_t>(stream));
+}
+
+int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
+                   float *device_ms, float *total_ms, rt_counters *counters) {
+  if (!scene_c) return fail(RT_ERR_INVALID, "scene is null");
+  if (!color || !t_inout) return fail(RT_ERR_INVALID, "color / t must not be null");
+  FrameDev fd;
+  int rc = make_frame(frame, fd);
+  if (rc) return rc;
+  rt_scene *s = const_cast<rt_scene *>(scene_c);
+  DeviceGuard g(s->device);
+  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
+  std::lock_guard<std::mutex> lock(s->host_mu);
+  const size_t pixels = (size_t)fd.W * fd.H, bytes = pixels * 4;
+  rc = ensure_host_buffers(s, pixels);
+  if (rc) return rc;
+  cudaStream_t st = s->h_stream;
+  RT_CUDA(cudaEventRecord(s->ev[0], st));
+  // the framebuffer is in/out (raytracing.cpp:17,90-94): pixels that are not overwritten keep the caller's values
+  RT_CUDA(cudaMemcpyAsync(s->h_t, t_inout, bytes, cudaMemcpyHostToDevice, st));
+  RT_CUDA(cudaMemcpyAsync(s->h_color, color, bytes, cudaMemcpyHostToDevice, st));
+  if (prim) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));
+  if (counters) RT_CUDA(cudaMemsetAsync(s->h_cnt, 0, sizeof(rt_counters), st));
+  RT_CUDA(cudaEventRecord(s->ev[1], st));
+  rc = render_on_stream(s, fd, s->h_color, s->h_t, s->h_t, prim ? s->h_prim : nullptr, counters ? s->h_cnt : nullptr, st);
+  if (rc) return rc;
+  RT_CUDA(cudaEventRecord(s->ev[2], st));
+  RT_CUDA(cudaMemcpyAsync(color, s->h_color, bytes, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaMemcpyAsync(t_inout, s->h_t, bytes, cudaMemcpyDeviceToHost, st));
+  if (prim) RT_CUDA(cudaMemcpyAsync(prim, s->h_prim, bytes, cudaMemcpyDeviceToHost, st));
+  if (counters) RT_CUDA(cudaMemcpyAsync(counters, s->h_cnt, sizeof(rt_counters), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaEventRecord(s->ev[3], st));
+  RT_CUDA(cudaStreamSynchronize(st));
+  if (device_ms) RT_CUDA(cudaEventElapsedTime(device_ms, s->ev[1], s->ev[2]));
+  if (total_ms) RT_CUDA(cudaEventElapsedTime(total_ms, s->ev[0], s->ev[3]));
+  return RT_OK;
+}
+
+int rt_intersect_host(const rt_scene *scene, const float *origins, const float *dirs, uint32_t n, float t_near,
+                      float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
+                      uint32_t *prim) {
+  if (!scene) return fail(RT_ERR_INVALID, "scene is null");
+  if (n == 0) return RT_OK;
+  if (!origins || !dirs) return fail(RT_ERR_INVALID, "origins / dirs must not be null");
+  DeviceGuard g(scene->device);
+  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
+  float *dO = nullptr, *dD = nullptr, *dT = nullptr, *dN = nullptr;
+  uint8_t *dH = nullptr;
+  uint32_t *dP = nullptr;
+  int rc = RT_OK;
+  auto cleanup = [&]() {
+    cudaFree(dO); cudaFree(dD); cudaFree(dT); cudaFree(dN); cudaFree(dH); cudaFree(dP);
+  };
+#define RT_TRY(call)                                     \
+  do {                                                   \
+    cudaError_t e__ = (call);                            \
+    if (e__ != cudaSuccess) { rc = cuda_fail(e__, #call); cleanup(); return rc; } \
+  } while (0)
+  RT_TRY(cudaMalloc(&dO, (size_t)n * 12));
+  RT_TRY(cudaMalloc(&dD, (size_t)n * 12));
+  RT_TRY(cudaMalloc(&dT, (size_t)n * 4));
+  RT_TRY(cudaMalloc(&dN, (size_t)n * 12));
+  RT_TRY(cudaMalloc(&dH, (size_t)n));
+  RT_TRY(cudaMalloc(&dP, (size_t)n * 4));
+  RT_TRY(cudaMemcpy(dO, origins, (size_t)n * 12, cudaMemcpyHostToDevice));
+  RT_TRY(cudaMemcpy(dD, dirs, (size_t)n * 12, cudaMemcpyHostToDevice));
+  RayArgs a;
+  a.scene = scene->dev;
+  a.origins = dO; a.dirs = dD; a.n = n;
+  a.t_near = t_near; a.t_far = t_far;
+  a.has_plane = has_plane != 0; a.plane_y = plane_y;
+  a.hit = dH; a.t = dT; a.normal = dN; a.prim = dP;
+  RT_TRY((g_math.load() == RT_MATH_FAST) ? fast::launch_rays(a, nullptr) : exact::launch_rays(a, nullptr));
+  RT_TRY(cudaDeviceSynchronize());
+  if (hit) RT_TRY(cudaMemcpy(hit, dH, (size_t)n, cudaMemcpyDeviceToHost));
+  if (t) RT_TRY(cudaMemcpy(t, dT, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  if (normal) RT_TRY(cudaMemcpy(normal, dN, (size_t)n * 12, cudaMemcpyDeviceToHost));
+  if (prim) RT_TRY(cudaMemcpy(prim, dP, (size_t)n * 4, cudaMemcpyDeviceToHost));
+#undef RT_TRY
+  cleanup();
+  return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,501 @@
+// Device-side restatement of the reference's per-ray arithmetic, written from scratch for one-thread-per-ray
+// execution (explicit stacks instead of recursion, per-thread loops instead of 8-lane ISPC calls).
+// Included inside `namespace rt::<flavour>`; the exact flavour is compiled with -fmad=false so that every
+// operator below is one correctly rounded IEEE-754 binary32 operation in the reference's operator order.
+// All file:line citations are into the reference tree.
+
+struct V3 {
+  float x, y, z;
+};
+
+// std::min/std::max (LiteMath.h:793-795 use them): FIRST argument unless the comparison says otherwise.
+// ISPC min/max (ray_pack.ispc:258-265) lower to minps/maxps: SECOND operand when either is NaN. SURVEY T11.
+__device__ __forceinline__ float std_min(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float std_max(float a, float b) { return (a < b) ? b : a; }
+__device__ __forceinline__ float ispc_min(float a, float b) { return a < b ? a : b; }
+__device__ __forceinline__ float ispc_max(float a, float b) { return a > b ? a : b; }
+
+__device__ __forceinline__ V3 mk3(float x, float y, float z) {
+  V3 r;
+  r.x = x; r.y = y; r.z = z;
+  return r;
+}
+__device__ __forceinline__ V3 add3(V3 a, V3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 sub3(V3 a, V3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 scale3(V3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// LiteMath.h:835-840 and ray_pack.ispc:12-20: shuffle_yzx(a*b_yzx - a_yzx*b)
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+  return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+// LiteMath.h:814: a * (1/length)
+__device__ __forceinline__ V3 lm_normalize(V3 a) {
+  float lenInv = 1.0f / sqrtf(dot3(a, a));
+  return scale3(a, lenInv);
+}
+// ray_pack.ispc:5-10: ray / length (three divisions)
+__device__ __forceinline__ V3 ispc_normalize(V3 r) {
+  float length = sqrtf(r.x * r.x + r.y * r.y + r.z * r.z);
+  return mk3(r.x / length, r.y / length, r.z / length);
+}
+// rayPos + t * rayDir as LiteMath evaluates it: componentwise product, then sum
+__device__ __forceinline__ V3 along(V3 o, V3 d, float t) { return mk3(o.x + d.x * t, o.y + d.y * t, o.z + d.z * t); }
+
+struct Hit {
+  bool hitten;
+  float t;
+  V3 normal;
+  float albedo;          // grey albedo: models (1,1,1), plane checker 0/1 (raytracing.hpp:67-73,160-163)
+  float reflectiveness;
+  uint32_t prim;
+};
+__device__ __forceinline__ Hit hit_none() {
+  Hit h;
+  h.hitten = false;
+  h.t = __int_as_float(0x7f800000);
+  h.normal = mk3(0.0f, 1.0f, 0.0f);
+  h.albedo = 1.0f;
+  h.reflectiveness = 0.0f;
+  h.prim = RT_PRIM_MISS;
+  return h;
+}
+
+struct Counters {
+  uint32_t grid_samples, oct_inner, oct_leaf, oct_leaf_samples, bvh_inner, bvh_leaf, bvh_tris, rays, hits;
+};
+
+// ---- LiteMath::BBox3f::Intersection (LiteMath.h:2005-2067) ------------------------------------------------
+__device__ __forceinline__ void bbox_intersection(V3 bmin, V3 bmax, V3 o, V3 inv, float min_t, float max_t, float &t1,
+                                                  float &t2) {
+  const float min_x = inv.x < 0 ? bmax.x : bmin.x;
+  const float min_y = inv.y < 0 ? bmax.y : bmin.y;
+  const float min_z = inv.z < 0 ? bmax.z : bmin.z;
+  const float max_x = inv.x < 0 ? bmin.x : bmax.x;
+  const float max_y = inv.y < 0 ? bmin.y : bmax.y;
+  const float max_z = inv.z < 0 ? bmin.z : bmax.z;
+  const float tmin_x = (min_x - o.x) * inv.x;
+  const float tmax_x = (max_x - o.x) * inv.x * 1.00000024f;
+  const float tmin_y = (min_y - o.y) * inv.y;
+  const float tmax_y = (max_y - o.y) * inv.y * 1.00000024f;
+  const float tmin_z = (min_z - o.z) * inv.z;
+  const float tmax_z = (max_z - o.z) * inv.z * 1.00000024f;
+  t2 = std_min(tmax_z, std_min(tmax_y, std_min(tmax_x, max_t)));
+  if (tmin_x > tmin_y) {
+    t1 = (tmin_z > tmin_x) ? std_max(tmin_z, min_t) : std_max(tmin_x, min_t);
+  } else {
+    t1 = (tmin_z > tmin_y) ? std_max(tmin_z, min_t) : std_max(tmin_y, min_t);
+  }
+}
+
+// ---- ispc::intersect_box_8, one lane (ray_pack.ispc:241-273) ---------------------------------------------
+__device__ __forceinline__ float slab_lane(float xMin, float yMin, float zMin, float xMax, float yMax, float zMax, V3 o,
+                                           V3 inv, float tNear, float tFar) {
+  float t1x = (xMin - o.x) * inv.x, t1y = (yMin - o.y) * inv.y, t1z = (zMin - o.z) * inv.z;
+  float t2x = (xMax - o.x) * inv.x, t2y = (yMax - o.y) * inv.y, t2z = (zMax - o.z) * inv.z;
+  float mnx = ispc_min(t1x, t2x), mny = ispc_min(t1y, t2y), mnz = ispc_min(t1z, t2z);
+  float mxx = ispc_max(t1x, t2x), mxy = ispc_max(t1y, t2y), mxz = ispc_max(t1z, t2z);
+  float tMin = ispc_max(mnx, ispc_max(mny, mnz));
+  float tMax = ispc_min(mxx, ispc_min(mxy, mxz));
+  tMin = ispc_max(tMin, tNear);
+  tMax = ispc_min(tMax, tFar);
+  if (tMax < 0 || tMin > tMax) return -1.0f;
+  return tMin;
+}
+
+// ---- sort8 (raytracing.hpp:188-213): the same 19 comparators in the same order, '>' compare ---------------
+#define RT_CSWAP(a, b)                  \
+  if (t[a] > t[b]) {                    \
+    float tf = t[a]; t[a] = t[b]; t[b] = tf; \
+    uint32_t tc = c[a]; c[a] = c[b]; c[b] = tc; \
+  }
+__device__ __forceinline__ void sort8(float (&t)[8], uint32_t (&c)[8]) {
+  RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(4, 5) RT_CSWAP(6, 7)
+  RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(4, 6) RT_CSWAP(5, 7)
+  RT_CSWAP(1, 2) RT_CSWAP(5, 6) RT_CSWAP(0, 4) RT_CSWAP(3, 7)
+  RT_CSWAP(1, 5) RT_CSWAP(2, 6)
+  RT_CSWAP(1, 4) RT_CSWAP(3, 6)
+  RT_CSWAP(2, 4) RT_CSWAP(3, 5)
+  RT_CSWAP(3, 4)
+}
+#undef RT_CSWAP
+
+// ---- Moeller-Trumbore, uniform ray x one triangle (ray_pack.ispc:132-165), without the normal: the normal
+// is a pure function of the triangle (:142) and is evaluated for the winner only ---------------------------
+__device__ __forceinline__ bool tri_lane(V3 o, V3 d, V3 v0, V3 v1, V3 v2, float &tOut) {
+  V3 e1 = sub3(v1, v0);
+  V3 e2 = sub3(v2, v0);
+  V3 pvec = cross3(d, e2);
+  float det = dot3(e1, pvec);
+  if (det < 1e-8f && det > -1e-8f) return false;
+  float inv_det = 1 / det;
+  V3 tvec = sub3(o, v0);
+  float u = dot3(tvec, pvec) * inv_det;
+  if (u < 0.0f || u > 1.0f) return false;
+  V3 qvec = cross3(tvec, e1);
+  float v = dot3(d, qvec) * inv_det;
+  if (v < 0.0f || u + v > 1.0f) return false;
+  tOut = dot3(e2, qvec) * inv_det;
+  return true;
+}
+__device__ __forceinline__ V3 ld3(const float4 &v) { return mk3(v.x, v.y, v.z); }
+
+// =============================================================================================================
+// Dense SDF grid (grid_raytracing.cpp)
+// =============================================================================================================
+__device__ __forceinline__ float grid_at(const GridDev &g, uint32_t x, uint32_t y, uint32_t z) {
+  if (g.bricks) {
+    // brick (x>>3, y>>3, z>>3), 512 floats per brick, same x-major / z-fastest order inside
+    size_t b = ((size_t)(x >> 3) * g.nby + (y >> 3)) * g.nbz + (z >> 3);
+    return __ldg(g.values + (b << 9) + (((x & 7u) << 6) | ((y & 7u) << 3) | (z & 7u)));
+  }
+  return __ldg(g.values + ((size_t)x * g.sy + y) * g.sz + z);  // grid_raytracing.hpp:13-15
+}
+
+// SDFGrid::sdf(float3), grid_raytracing.cpp:7-62; cell = linear index of corner c0 (the grid's "prim id")
+template <bool COUNT>
+__device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell, Counters &cnt) {
+  if (COUNT) cnt.grid_samples++;
+  p.x = (p.x + 1.0f) / 2.0f; p.y = (p.y + 1.0f) / 2.0f; p.z = (p.z + 1.0f) / 2.0f;
+  p.x *= (float)(g.sx - 1); p.y *= (float)(g.sy - 1); p.z *= (float)(g.sz - 1);
+  float c0fx = floorf(p.x), c0fy = floorf(p.y), c0fz = floorf(p.z);
+  float c1fx = ceilf(p.x), c1fy = ceilf(p.y), c1fz = ceilf(p.z);
+  uint32_t c0x = (uint32_t)c0fx, c0y = (uint32_t)c0fy, c0z = (uint32_t)c0fz;
+  uint32_t c1x = (uint32_t)c1fx, c1y = (uint32_t)c1fy, c1z = (uint32_t)c1fz;
+  float px = p.x - c0fx, py = p.y - c0fy, pz = p.z - c0fz;  // p_c0f
+  float qx = c1fx - p.x, qy = c1fy - p.y, qz = c1fz - p.z;  // c1f_p
+  if (c1x == c0x) { px = 1.0f; qx = 0.0f; }                 // :25-38
+  if (c1y == c0y) { py = 1.0f; qy = 0.0f; }
+  if (c1z == c0z) { pz = 1.0f; qz = 0.0f; }
+  float v0 = grid_at(g, c0x, c0y, c0z), v1 = grid_at(g, c0x, c0y, c1z);
+  float v2 = grid_at(g, c0x, c1y, c0z), v3 = grid_at(g, c0x, c1y, c1z);
+  float v4 = grid_at(g, c1x, c0y, c0z), v5 = grid_at(g, c1x, c0y, c1z);
+  float v6 = grid_at(g, c1x, c1y, c0z), v7 = grid_at(g, c1x, c1y, c1z);
+  float res = 0.0f;
+  res += v0 * qx * qy * qz;
+  res += v1 * qx * qy * pz;
+  res += v2 * qx * py * qz;
+  res += v3 * qx * py * pz;
+  res += v4 * px * qy * qz;
+  res += v5 * px * qy * pz;
+  res += v6 * px * py * qz;
+  res += v7 * px * py * pz;
+  cell = (uint32_t)(((size_t)c0x * g.sy + c0y) * g.sz + c0z);
+  return res;
+}
+
+// SDFGrid::normal, grid_raytracing.cpp:64-89: clamped +-1e-3 differences, not scaled, then normalize
+template <bool COUNT>
+__device__ __forceinline__ V3 grid_normal(const GridDev &g, V3 p, Counters &cnt) {
+  const float E = 1e-3f;
+  float xL = (p.x - E >= -1.0f) ? p.x - E : p.x, xR = (p.x + E <= 1.0f) ? p.x + E : p.x;
+  float yL = (p.y - E >= -1.0f) ? p.y - E : p.y, yR = (p.y + E <= 1.0f) ? p.y + E : p.y;
+  float zL = (p.z - E >= -1.0f) ? p.z - E : p.z, zR = (p.z + E <= 1.0f) ? p.z + E : p.z;
+  uint32_t c;
+  float dx = grid_sdf<COUNT>(g, mk3(xR, p.y, p.z), c, cnt) - grid_sdf<COUNT>(g, mk3(xL, p.y, p.z), c, cnt);
+  float dy = grid_sdf<COUNT>(g, mk3(p.x, yR, p.z), c, cnt) - grid_sdf<COUNT>(g, mk3(p.x, yL, p.z), c, cnt);
+  float dz = grid_sdf<COUNT>(g, mk3(p.x, p.y, zR), c, cnt) - grid_sdf<COUNT>(g, mk3(p.x, p.y, zL), c, cnt);
+  return lm_normalize(mk3(dx, dy, dz));
+}
+
+// SDFGrid::intersect, grid_raytracing.cpp:93-125
+template <bool COUNT>
+__device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  Hit r = hit_none();
+  V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  float t1, t2;
+  bbox_intersection(mk3(-1.0f, -1.0f, -1.0f), mk3(1.0f, 1.0f, 1.0f), o, inv, tNear, tFar, t1, t2);
+  if (t1 > t2) return r;
+  float t = t1;
+  V3 p = along(o, d, t);
+  p.x = std_max(p.x, -1.0f); p.y = std_max(p.y, -1.0f); p.z = std_max(p.z, -1.0f);
+  p.x = std_min(p.x, 1.0f); p.y = std_min(p.y, 1.0f); p.z = std_min(p.z, 1.0f);
+  while (p.x <= 1.0f && p.y <= 1.0f && p.z <= 1.0f && p.x >= -1.0f && p.y >= -1.0f && p.z >= -1.0f) {
+    uint32_t cell;
+    float sd = grid_sdf<COUNT>(g, p, cell, cnt);
+    if (sd < 1e-3f) {
+      r.hitten = true;
+      r.t = t + sd;
+      r.normal = grid_normal<COUNT>(g, p, cnt);
+      r.prim = cell;
+      break;
+    }
+    t += sd;
+    p = along(o, d, t);
+  }
+  return r;
+}
+
+// =============================================================================================================
+// SDF octree (octree_raytracing.cpp)
+// =============================================================================================================
+// SDFOctree::nodeSDF(float3), octree_raytracing.cpp:18-57.  The local coordinate is clamped to
+// [1e-7, 0.9999999] so floor/ceil are always 0/1: c0 = 0, c1 = 1, p_c0f = u, c1f_p = 1 - u.
+// (p - min) / (max - min): the extent is a power of two, so multiplying by its reciprocal is the same
+// correctly rounded result as the reference's division.
+__device__ __forceinline__ void oct_local(V3 bmin, float invExt, V3 p, float (&pc)[3], float (&cp)[3]) {
+  float q[3] = {(p.x - bmin.x) * invExt, (p.y - bmin.y) * invExt, (p.z - bmin.z) * invExt};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float u = std_min(std_max(0.0000001f, q[i]), 0.9999999f);  // LiteMath clamp = min(max(a,u),b), LiteMath.h:97
+    pc[i] = u - 0.0f;
+    cp[i] = 1.0f - u;
+  }
+}
+
+__device__ __forceinline__ float oct_node_sdf(const float (&v)[8], V3 bmin, float invExt, V3 p) {
+  float pc[3], cp[3];
+  oct_local(bmin, invExt, p, pc, cp);
+  float res = 0.0f;
+  res += v[0] * cp[0] * cp[1] * cp[2];
+  res += v[1] * cp[0] * cp[1] * pc[2];
+  res += v[2] * cp[0] * pc[1] * cp[2];
+  res += v[3] * cp[0] * pc[1] * pc[2];
+  res += v[4] * pc[0] * cp[1] * cp[2];
+  res += v[5] * pc[0] * cp[1] * pc[2];
+  res += v[6] * pc[0] * pc[1] * cp[2];
+  res += v[7] * pc[0] * pc[1] * pc[2];
+  return res;
+}
+
+// SDFOctree::nodeNormal, octree_raytracing.cpp:59-118: analytic gradient of the same trilinear form
+__device__ __forceinline__ V3 oct_node_normal(const float (&v)[8], V3 bmin, float invExt, V3 p) {
+  float pc[3], cp[3];
+  oct_local(bmin, invExt, p, pc, cp);
+  const float dp = 1.0f, dc = -1.0f;  // dp_c0f, dc1f_p
+  float dfdx = v[0] * dc * cp[1] * cp[2] + v[1] * dc * cp[1] * pc[2] + v[2] * dc * pc[1] * cp[2] +
+               v[3] * dc * pc[1] * pc[2] + v[4] * dp * cp[1] * cp[2] + v[5] * dp * cp[1] * pc[2] +
+               v[6] * dp * pc[1] * cp[2] + v[7] * dp * pc[1] * pc[2];
+  float dfdy = v[0] * cp[0] * dc * cp[2] + v[1] * cp[0] * dc * pc[2] + v[2] * cp[0] * dp * cp[2] +
+               v[3] * cp[0] * dp * pc[2] + v[4] * pc[0] * dc * cp[2] + v[5] * pc[0] * dc * pc[2] +
+               v[6] * pc[0] * dp * cp[2] + v[7] * pc[0] * dp * pc[2];
+  float dfdz = v[0] * cp[0] * cp[1] * dc + v[1] * cp[0] * cp[1] * dp + v[2] * cp[0] * pc[1] * dc +
+               v[3] * cp[0] * pc[1] * dp + v[4] * pc[0] * cp[1] * dc + v[5] * pc[0] * cp[1] * dp +
+               v[6] * pc[0] * pc[1] * dc + v[7] * pc[0] * pc[1] * dp;
+  return lm_normalize(mk3(dfdx, dfdy, dfdz));
+}
+
+// SDFOctree::intersectLeaf, octree_raytracing.cpp:122-164, for a leaf that survived the value culls
+template <bool COUNT>
+__device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 bmin, float ext, V3 o, V3 d, V3 inv,
+                                         float tNear, float tFar, Hit &r, Counters &cnt) {
+  V3 bmax = mk3(bmin.x + ext, bmin.y + ext, bmin.z + ext);
+  float t1, t2;
+  bbox_intersection(bmin, bmax, o, inv, tNear, tFar, t1, t2);
+  if (t1 > t2) return false;
+  const float4 a = __ldg(oc.values + 2 * (size_t)node), b = __ldg(oc.values + 2 * (size_t)node + 1);
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  const float invExt = 1.0f / ext;
+  float t = t1;
+  V3 p = along(o, d, t);
+  p.x = std_max(p.x, bmin.x); p.y = std_max(p.y, bmin.y); p.z = std_max(p.z, bmin.z);
+  p.x = std_min(p.x, bmax.x); p.y = std_min(p.y, bmax.y); p.z = std_min(p.z, bmax.z);
+  while (p.x <= bmax.x && p.y <= bmax.y && p.z <= bmax.z && p.x >= bmin.x && p.y >= bmin.y && p.z >= bmin.z) {
+    if (COUNT) cnt.oct_leaf_samples++;
+    float sd = oct_node_sdf(v, bmin, invExt, p);
+    if (sd < 1e-4f) {
+      r.hitten = true;
+      r.t = t + sd;
+      r.normal = oct_node_normal(v, bmin, invExt, p);
+      r.prim = node;
+      return true;
+    }
+    t += sd;
+    p = along(o, d, t);
+  }
+  return false;
+}
+
+// SDFOctree::intersectNode, octree_raytracing.cpp:166-202, as an explicit-stack ordered descent.
+// The reference recursion returns as soon as ANY leaf reports a hit (the first hitting child ends every
+// enclosing loop, :188-197), so `hit.t > t` is never evaluated with a hit in hand: the visit rule is just
+// t > 0 in sort8 order.  Per level we keep one word: the not-yet-visited children in visit order, 4 bits each
+// (bit 3 = valid), and the node's childrenOffset.  Child boxes come from integer (level, i, j, k): the dyadic
+// subdivision of [-1,1] that divide_box_8 (ray_pack.ispc:220-239) computes is exact.
+template <bool COUNT>
+__device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  Hit r = hit_none();
+  const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  uint32_t pend[OCT_MAX_DEPTH + 1];   // pending children of the node at each level
+  uint32_t base[OCT_MAX_DEPTH + 1];   // its childrenOffset
+  int level = 0;                      // level of `node`
+  uint32_t node = 0, ix = 0, iy = 0, iz = 0;
+  float ext = 2.0f;                   // edge of the current node's box
+  for (;;) {
+    // ---- visit `node` at (level, ix, iy, iz)
+    const uint32_t link = __ldg(oc.link + node);
+    const V3 bmin = mk3(-1.0f + (float)ix * ext, -1.0f + (float)iy * ext, -1.0f + (float)iz * ext);
+    bool descend = false;
+    if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
+      if (COUNT) cnt.oct_leaf++;
+      if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, node, bmin, ext, o, d, inv, tNear, tFar, r, cnt)) return r;
+    } else {
+      if (COUNT) cnt.oct_inner++;
+      const float h = ext * 0.5f;
+      const V3 c = mk3(bmin.x + h, bmin.y + h, bmin.z + h);  // (min+max)/2, exact
+      float ts[8];
+      uint32_t ch[8];
+#pragma unroll
+      for (int id = 0; id < 8; ++id) {
+        const float mx = (id & 4) ? c.x : bmin.x, my = (id & 2) ? c.y : bmin.y, mz = (id & 1) ? c.z : bmin.z;
+        ts[id] = slab_lane(mx, my, mz, mx + h, my + h, mz + h, o, inv, tNear, tFar);
+        ch[id] = id;
+      }
+      sort8(ts, ch);
+      uint32_t w = 0;
+#pragma unroll
+      for (int i = 7; i >= 0; --i)
+        if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
+      if (w) {
+        pend[level] = w;
+        base[level] = link;
+        descend = true;
+      }
+    }
+    if (!descend) {
+      // ---- climb to the deepest ancestor that still has pending children
+      for (;;) {
+        if (level == 0) return r;
+        --level;
+        ix >>= 1; iy >>= 1; iz >>= 1;
+        ext *= 2.0f;
+        if (pend[level]) break;
+      }
+    }
+    const uint32_t w = pend[level];
+    const uint32_t id = w & 7u;
+    pend[level] = w >> 4;
+    node = base[level] + id;
+    ix = (ix << 1) | (id >> 2);
+    iy = (iy << 1) | ((id >> 1) & 1u);
+    iz = (iz << 1) | (id & 1u);
+    ext *= 0.5f;
+    ++level;
+  }
+}
+
+// =============================================================================================================
+// Triangle mesh: 8-wide BVH (triangles_raytracing.cpp:266-335) and brute force (ray_pack.ispc:167-202)
+// =============================================================================================================
+// BVHBuilder::traverseNode as an explicit-stack closest-hit traversal.  Children are pushed far-to-near in
+// sort8 order so they pop in the reference's visit order; the cull `hit && hit.t < t_entry` (:282-284) is
+// evaluated at pop time against the best hit so far.  (The recursion culls against the best hit of the
+// enclosing node only; a subtree it visits and we skip starts behind the current best hit, so it cannot
+// change the closest hit — DESIGN.md "BVH culling".)  Ties keep the first hit in visit order (strict '>').
+template <bool COUNT>
+__device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  Hit r = hit_none();
+  const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  uint32_t stackRef[BVH_STACK];
+  float stackT[BVH_STACK];
+  int sp = 0;
+  uint32_t bestTri = 0;
+  uint32_t ref = 0;  // root is always an inner node
+  for (;;) {
+    if (!(ref & BVH_LEAF_BIT)) {
+      if (COUNT) cnt.bvh_inner++;
+      const float4 *n4 = reinterpret_cast<const float4 *>(m.nodes + ref);
+      float b[48];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) {
+        float4 q = __ldg(n4 + i);
+        b[4 * i] = q.x; b[4 * i + 1] = q.y; b[4 * i + 2] = q.z; b[4 * i + 3] = q.w;
+      }
+      const uint4 c0 = __ldg(reinterpret_cast<const uint4 *>(n4 + 12)), c1 = __ldg(reinterpret_cast<const uint4 *>(n4 + 13));
+      const uint32_t child[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+      float t[8];
+      uint32_t ch[8];  // sort8 payload = the child word itself (the reference sorts child indices)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float ti = slab_lane(b[i], b[8 + i], b[16 + i], b[24 + i], b[32 + i], b[40 + i], o, inv, tNear, tFar);
+        t[i] = (child[i] == BVH_EMPTY) ? -1.0f : ti;  // unused lanes behave as misses
+        ch[i] = child[i];
+      }
+      sort8(t, ch);
+#pragma unroll
+      for (int i = 7; i >= 0; --i) {
+        if (!(t[i] < 0)) {  // :282-284 skips t < 0 (slab_lane never returns NaN: tNear wins every max)
+          stackRef[sp] = ch[i];  // depth of the stack is validated against BVH_STACK at scene creation
+          stackT[sp] = t[i];
+          ++sp;
+        }
+      }
+    } else {
+      if (COUNT) cnt.bvh_leaf++;
+      const uint32_t first = ref & 0x07FFFFFFu, count = ((ref >> 27) & 15u) + 1u;
+      for (uint32_t k = 0; k < count; ++k) {
+        if (COUNT) cnt.bvh_tris++;
+        const float4 *tp = reinterpret_cast<const float4 *>(m.tris + first + k);
+        const float4 a = __ldg(tp), bq = __ldg(tp + 1), cq = __ldg(tp + 2);
+        float th;
+        if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && (!r.hitten || r.t > th)) {
+          r.hitten = true;
+          r.t = th;
+          bestTri = first + k;
+        }
+      }
+    }
+    // ---- pop the next subtree that can still hold a closer hit
+    for (;;) {
+      if (sp == 0) goto done;
+      --sp;
+      ref = stackRef[sp];
+      if (!(r.hitten && r.t < stackT[sp])) break;
+    }
+  }
+done:
+  if (r.hitten) {
+    const float4 *tp = reinterpret_cast<const float4 *>(m.tris + bestTri);
+    const float4 a = __ldg(tp), bq = __ldg(tp + 1), cq = __ldg(tp + 2);
+    r.normal = ispc_normalize(cross3(sub3(ld3(bq), ld3(a)), sub3(ld3(cq), ld3(a))));  // ray_pack.ispc:142
+    r.prim = __float_as_uint(a.w);
+  }
+  return r;
+}
+
+// Every triangle against the ray, triangles staged in shared memory by the kernel (smem = n_tris x 3 float4).
+template <bool COUNT>
+__device__ __forceinline__ Hit brute_intersect(const float4 *smemTris, uint32_t nTris, V3 o, V3 d, Counters &cnt) {
+  Hit r = hit_none();
+  uint32_t best = 0;
+  for (uint32_t k = 0; k < nTris; ++k) {
+    if (COUNT) cnt.bvh_tris++;
+    const float4 a = smemTris[3 * k], bq = smemTris[3 * k + 1], cq = smemTris[3 * k + 2];
+    float th;
+    if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && (!r.hitten || r.t > th)) {
+      r.hitten = true;
+      r.t = th;
+      best = k;
+    }
+  }
+  if (r.hitten) {
+    const float4 a = smemTris[3 * best], bq = smemTris[3 * best + 1], cq = smemTris[3 * best + 2];
+    r.normal = ispc_normalize(cross3(sub3(ld3(bq), ld3(a)), sub3(ld3(cq), ld3(a))));
+    r.prim = __float_as_uint(a.w);
+  }
+  return r;
+}
+
+// =============================================================================================================
+// Plane({0,1,0}, planeY) (raytracing.hpp:119-186) and SceneUnion (raytracing.hpp:83-97)
+// =============================================================================================================
+__device__ __forceinline__ Hit plane_intersect(float planeY, V3 o, V3 d, float tNear, float tFar) {
+  Hit r = hit_none();
+  const V3 n = mk3(0.0f, 1.0f, 0.0f);
+  // recalcBasis() for this normal: b1 = normalize({0, n.z, -n.y}), b2 = normalize(cross(b1, n))
+  const V3 b1 = lm_normalize(mk3(0.0f, n.z, -n.y));
+  const V3 b2 = lm_normalize(cross3(b1, n));
+  float dividor = dot3(d, n);
+  if (fabsf(dividor) < 1e-8f) return r;
+  float t = (planeY - dot3(o, n)) / dividor;
+  if (t < tNear || t > tFar) return r;
+  V3 p = along(o, d, t);
+  int x = (int)ceilf(dot3(p, b1));
+  int y = (int)ceilf(dot3(p, b2));
+  r.hitten = true;
+  r.t = t;
+  r.normal = n;
+  r.albedo = ((x + y) % 2 == 0) ? 0.0f : 1.0f;
+  r.reflectiveness = 0.3f;
+  r.prim = RT_PRIM_PLANE;
+  return r;
+}

@@ -1,0 +1,341 @@
+// Render kernels: per-pixel eye ray -> scene intersect -> shade -> pack -> depth-tested write, i.e. the body of
+// Renderer::draw's pixel loop (raytracing.cpp:80-95) and Renderer::intersectionColor (:13-65), one thread per ray.
+// This file is compiled twice (rt_kernels_exact.cu with -fmad=false, rt_kernels_fast.cu with FMA contraction),
+// each time into its own namespace RT_NS.
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "rt_scene.h"
+
+namespace rt {
+namespace RT_NS {
+
+#include "rt_device.cuh"
+
+constexpr int KIND_GRID = 0, KIND_OCTREE = 1, KIND_BVH = 2, KIND_BRUTE = 3;
+constexpr int BLOCK_THREADS = 256;
+// a warp owns an 8x4 pixel tile; a 256-thread block owns 32x8 pixels (4 warps across, 2 down)
+constexpr int TILE_W = 8, TILE_H = 4;
+
+// IScene::intersect of the model, and of SceneUnion(model, plane) (raytracing.hpp:83-97)
+template <int KIND, bool COUNT>
+__device__ __forceinline__ Hit model_intersect(const SceneDev &s, const float4 *smemTris, V3 o, V3 d, float tNear,
+                                               float tFar, Counters &cnt) {
+  if (COUNT) cnt.rays++;
+  if (KIND == KIND_GRID) return grid_intersect<COUNT>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_OCTREE) return oct_intersect<COUNT>(s.oct, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_BVH) return bvh_intersect<COUNT>(s.mesh, o, d, tNear, tFar, cnt);
+  return brute_intersect<COUNT>(smemTris, s.mesh.n_tris, o, d, cnt);
+}
+
+template <int KIND, bool COUNT>
+__device__ __forceinline__ Hit scene_intersect(const SceneDev &s, const float4 *smemTris, bool hasPlane, float planeY,
+                                               V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  Hit a = model_intersect<KIND, COUNT>(s, smemTris, o, d, tNear, tFar, cnt);
+  if (!hasPlane) return a;
+  Hit b = plane_intersect(planeY, o, d, tNear, tFar);
+  return (a.t < b.t) ? a : b;
+}
+
+// the secondary-ray variant calls through one out-of-line copy so the traversal code is not inlined 4 times
+template <int KIND, bool COUNT>
+__device__ __noinline__ Hit scene_intersect_shared(const SceneDev &s, const float4 *smemTris, bool hasPlane,
+                                                   float planeY, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  return scene_intersect<KIND, COUNT>(s, smemTris, hasPlane, planeY, o, d, tNear, tFar, cnt);
+}
+
+// raytracing.cpp:82-88 + EyeRayDir4f (LiteMath.h:2121-2134) + mat4_colmajor_mul_vec4 (:1371-1377).
+// (x, y) are the LOOP coordinates of Renderer::draw: y = 0 is the bottom of the view.
+__device__ __forceinline__ V3 eye_ray(const FrameDev &f, int x, int y) {
+  float fx = (float)x + 0.5f, fy = (float)y + 0.5f;
+  float w = (float)f.W, h = (float)f.H;
+  float V0 = 2.0f * (fx + 0.5f) / w - 1.0f, V1 = -2.0f * (fy + 0.5f) / h + 1.0f, V2 = 0.0f, V3_ = 1.0f;
+  const float *B = f.proj_inv;
+  float pos[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pos[i] = V0 * B[i] + V1 * B[4 + i] + V2 * B[8 + i] + V3_ * B[12 + i];
+  float pw = pos[3];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pos[i] = pos[i] / pw;
+  pos[1] *= (-1.0f);
+  float lenInv = 1.0f / sqrtf(pos[0] * pos[0] + pos[1] * pos[1] + pos[2] * pos[2]);
+  float D0 = pos[0] * lenInv, D1 = pos[1] * lenInv, D2 = pos[2] * lenInv, D3 = 0.0f;
+  const float *M = f.view_inv;
+  return mk3(D0 * M[0] + D1 * M[4] + D2 * M[8] + D3 * M[12], D0 * M[1] + D1 * M[5] + D2 * M[9] + D3 * M[13],
+             D0 * M[2] + D1 * M[6] + D2 * M[10] + D3 * M[14]);
+}
+
+struct C4 {
+  float r, g, b, a;
+};
+// LiteMath.h:1741-1746 + to_uint32 :1153 (truncation)
+__device__ __forceinline__ uint32_t color_pack_rgba(C4 c) {
+  uint32_t r = (uint32_t)(c.r * 255.0f), g = (uint32_t)(c.g * 255.0f), b = (uint32_t)(c.b * 255.0f),
+           a = (uint32_t)(c.a * 255.0f);
+  return (a << 24) | (b << 16) | (g << 8) | r;
+}
+
+// Lambert branch of intersectionColor for one hit (raytracing.cpp:33-50); `visible` = shadow-ray result
+__device__ __forceinline__ C4 lambert_color(const Hit &hit, V3 point, V3 light, bool visible) {
+  C4 c;
+  if (!visible) {
+    c.r = c.g = c.b = hit.albedo * 0.1f;
+  } else {
+    V3 ldir = lm_normalize(sub3(point, light));
+    float lam = std_max(dot3(mk3(-ldir.x, -ldir.y, -ldir.z), hit.normal), 0.0f);
+    c.r = c.g = c.b = std_min(hit.albedo * 0.1f + lam * hit.albedo, 1.0f);
+  }
+  c.a = 1.0f;
+  return c;
+}
+
+// Renderer::intersectionColor (raytracing.cpp:13-65) for a primary ray. Returns false on a miss.
+template <int KIND, bool COUNT, bool SECONDARY>
+__device__ __forceinline__ bool intersection_color(const SceneDev &s, const FrameDev &f, const float4 *smemTris, V3 o,
+                                                   V3 d, float tPrev, C4 &color, float &tOut, uint32_t &primOut,
+                                                   Counters &cnt) {
+  const bool plane = f.has_plane != 0;
+  Hit hit = SECONDARY ? scene_intersect_shared<KIND, COUNT>(s, smemTris, plane, f.plane_y, o, d, f.t_near,
+                                                           std_min(f.t_far, tPrev), cnt)
+                      : scene_intersect<KIND, COUNT>(s, smemTris, plane, f.plane_y, o, d, f.t_near,
+                                                     std_min(f.t_far, tPrev), cnt);
+  if (!hit.hitten) return false;
+  if (COUNT) cnt.hits++;
+  if (dot3(hit.normal, d) > 0) hit.normal = scale3(hit.normal, -1.0f);
+  if (f.mode == RT_SHADE_NORMAL) {
+    color.r = (hit.normal.x + 1.0f) / 2.0f;
+    color.g = (hit.normal.y + 1.0f) / 2.0f;
+    color.b = (hit.normal.z + 1.0f) / 2.0f;
+    color.a = (1.0f + 1.0f) / 2.0f;
+  } else if (f.mode == RT_SHADE_COLOR) {
+    color.r = color.g = color.b = hit.albedo;
+    color.a = 1.0f;
+  } else {
+    const V3 light = mk3(f.light[0], f.light[1], f.light[2]);
+    const V3 point = along(o, d, hit.t);
+    bool visible = true;
+    if (SECONDARY && f.shadows) {
+      V3 sdir = lm_normalize(sub3(light, point));
+      Hit sh = scene_intersect_shared<KIND, COUNT>(s, smemTris, plane, f.plane_y, along(point, sdir, 0.3f), sdir, 0.01f,
+                                                   100.0f, cnt);
+      visible = !sh.hitten;
+    }
+    color = lambert_color(hit, point, light, visible);
+    if (SECONDARY && f.reflections && hit.reflectiveness > 0.0f) {
+      // reflect(dir, n) = n * dot(dir, n) * (-2) + dir, LiteMath.h:1196; one bounce (maxDepth 2)
+      float dn = dot3(d, hit.normal);
+      V3 rdir = lm_normalize(mk3(hit.normal.x * dn * (-2.0f) + d.x, hit.normal.y * dn * (-2.0f) + d.y,
+                                 hit.normal.z * dn * (-2.0f) + d.z));
+      V3 ro = along(point, rdir, 0.02f);
+      C4 rc;
+      rc.r = rc.g = rc.b = 0.0f;
+      rc.a = 1.0f;
+      Hit h2 = scene_intersect_shared<KIND, COUNT>(s, smemTris, plane, f.plane_y, ro, rdir, 0.01f,
+                                                   std_min(100.0f, __int_as_float(0x7f800000)), cnt);
+      if (h2.hitten) {
+        if (COUNT) cnt.hits++;
+        if (dot3(h2.normal, rdir) > 0) h2.normal = scale3(h2.normal, -1.0f);
+        V3 p2 = along(ro, rdir, h2.t);
+        bool vis2 = true;
+        if (f.shadows) {
+          V3 sdir = lm_normalize(sub3(light, p2));
+          Hit sh = scene_intersect_shared<KIND, COUNT>(s, smemTris, plane, f.plane_y, along(p2, sdir, 0.3f), sdir,
+                                                       0.01f, 100.0f, cnt);
+          vis2 = !sh.hitten;
+        }
+        rc = lambert_color(h2, p2, light, vis2);
+      }
+      const float k = hit.reflectiveness, ik = 1.0f - hit.reflectiveness;
+      color.r = color.r * ik + k * rc.r;
+      color.g = color.g * ik + k * rc.g;
+      color.b = color.b * ik + k * rc.b;
+      color.a = color.a * ik + k * rc.a;
+    }
+  }
+  tOut = hit.t;
+  primOut = hit.prim;
+  return true;
+}
+
+__device__ __forceinline__ void flush_counters(const Counters &c, unsigned long long *g) {
+  // order = rt_counters: rays, hits, grid_samples, oct_inner, oct_leaf, oct_leaf_samples, bvh_inner, bvh_leaf, bvh_tris
+  const uint32_t v[9] = {c.rays, c.hits, c.grid_samples, c.oct_inner, c.oct_leaf, c.oct_leaf_samples,
+                         c.bvh_inner, c.bvh_leaf, c.bvh_tris};
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    uint32_t x = v[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if ((threadIdx.x & 31) == 0 && x) atomicAdd(g + i, (unsigned long long)x);
+  }
+}
+
+// stage the whole triangle list in shared memory (brute-force scenes; 48 B per triangle, float4 loads)
+__device__ __forceinline__ void stage_triangles(const MeshDev &m, float4 *smemTris) {
+  const float4 *src = reinterpret_cast<const float4 *>(m.tris);
+  for (uint32_t i = threadIdx.x; i < 3 * m.n_tris; i += blockDim.x) smemTris[i] = __ldg(src + i);
+  __syncthreads();
+}
+
+// one pixel: memory row `row` (0 = top), column x
+template <int KIND, bool COUNT, bool SECONDARY>
+__device__ __forceinline__ void shade_pixel(const RenderArgs &a, const float4 *smemTris, uint32_t x, uint32_t row,
+                                            Counters &cnt) {
+  const FrameDev &f = a.frame;
+  const size_t px = (size_t)row * f.W + x;
+  const int y = (int)(f.H - 1u - row);  // loop coordinate of raytracing.cpp:80-82
+  const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
+  const V3 d = eye_ray(f, (int)x, y);
+  const float tPrev = a.t_in ? a.t_in[px] : __int_as_float(0x7f800000);
+  C4 col;
+  float tNew;
+  uint32_t prim;
+  if (intersection_color<KIND, COUNT, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
+      !isinf(tNew)) {
+    a.t_out[px] = tNew;
+    a.color[px] = color_pack_rgba(col);
+    if (a.prim) a.prim[px] = prim;
+  }
+}
+
+// virtual row v (0 .. rows_here) of this call -> memory row of the frame (interleaved bands, rt_frame)
+__device__ __forceinline__ uint32_t band_row(const FrameDev &f, uint32_t v) {
+  if (f.band_count <= 1u) return v;
+  const uint32_t b = v / f.band_rows, r = v - b * f.band_rows;
+  return (b * f.band_count + f.band_index) * f.band_rows + r;
+}
+
+// ---- RT_SCHED_TILES: one thread per pixel -------------------------------------------------------------------
+template <int KIND, bool COUNT, bool SECONDARY>
+__global__ void __launch_bounds__(BLOCK_THREADS) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
+  extern __shared__ float4 smemTris[];
+  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t x = blockIdx.x * 32u + (warp & 3u) * TILE_W + (lane & 7u);
+  const uint32_t v = blockIdx.y * 8u + (warp >> 2) * TILE_H + (lane >> 3);
+  Counters cnt = {};
+  if (x < a.frame.W && v < a.frame.rows_here) {
+    const uint32_t row = band_row(a.frame, v);
+    if (row < a.frame.H) shade_pixel<KIND, COUNT, SECONDARY>(a, smemTris, x, row, cnt);
+  }
+  if (COUNT) flush_counters(cnt, a.counters);
+}
+
+// ---- RT_SCHED_PERSISTENT: persistent warps, dynamic tile fetch ------------------------------------------------
+// Each warp repeatedly takes the next 8x4 tile from a global counter, so warps whose rays all terminate early
+// (box misses cost a few dozen instructions) immediately pick up new work instead of idling until the slowest
+// warp of their block finishes; the grid is sized to the machine (sm_count x resident blocks).
+template <int KIND, bool COUNT, bool SECONDARY>
+__global__ void __launch_bounds__(BLOCK_THREADS) render_persistent_kernel(const __grid_constant__ RenderArgs a) {
+  extern __shared__ float4 smemTris[];
+  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t tilesX = (a.frame.W + TILE_W - 1) / TILE_W, tilesY = (a.frame.rows_here + TILE_H - 1) / TILE_H;
+  const uint32_t nTiles = tilesX * tilesY;
+  Counters cnt = {};
+  for (;;) {
+    uint32_t tile = 0;
+    if (lane == 0) tile = atomicAdd(a.tile_counter, 1u);
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+    if (tile >= nTiles) break;
+    const uint32_t ty = tile / tilesX, tx = tile - ty * tilesX;
+    const uint32_t x = tx * TILE_W + (lane & 7u), v = ty * TILE_H + (lane >> 3);
+    if (x < a.frame.W && v < a.frame.rows_here) {
+      const uint32_t row = band_row(a.frame, v);
+      if (row < a.frame.H) shade_pixel<KIND, COUNT, SECONDARY>(a, smemTris, x, row, cnt);
+    }
+  }
+  if (COUNT) flush_counters(cnt, a.counters);
+}
+
+// ---- IScene::intersect for n arbitrary rays ---------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(BLOCK_THREADS) rays_kernel(const __grid_constant__ RayArgs a) {
+  extern __shared__ float4 smemTris[];
+  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  Counters cnt = {};
+  const V3 o = mk3(a.origins[3 * i], a.origins[3 * i + 1], a.origins[3 * i + 2]);
+  const V3 d = mk3(a.dirs[3 * i], a.dirs[3 * i + 1], a.dirs[3 * i + 2]);
+  Hit h = scene_intersect<KIND, false>(a.scene, smemTris, a.has_plane != 0, a.plane_y, o, d, a.t_near, a.t_far, cnt);
+  if (a.hit) a.hit[i] = h.hitten ? 1 : 0;
+  if (a.t) a.t[i] = h.t;
+  if (a.normal) {
+    a.normal[3 * i] = h.normal.x;
+    a.normal[3 * i + 1] = h.normal.y;
+    a.normal[3 * i + 2] = h.normal.z;
+  }
+  if (a.prim) a.prim[i] = h.prim;
+}
+
+// ---- launchers ------------------------------------------------------------------------------------------------
+static inline int kind_of(const SceneDev &s) {
+  if (s.kind == RT_SCENE_GRID) return KIND_GRID;
+  if (s.kind == RT_SCENE_OCTREE) return KIND_OCTREE;
+  return s.mesh.brute ? KIND_BRUTE : KIND_BVH;
+}
+
+template <int KIND, bool COUNT, bool SECONDARY>
+static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count, cudaStream_t st) {
+  const size_t smem = (KIND == KIND_BRUTE) ? (size_t)a.scene.mesh.n_tris * sizeof(TriDev) : 0;
+  if (sched == RT_SCHED_PERSISTENT) {
+    auto kern = render_persistent_kernel<KIND, COUNT, SECONDARY>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int perSm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, BLOCK_THREADS, smem);
+    if (e != cudaSuccess) return e;
+    if (perSm < 1) perSm = 1;
+    e = cudaMemsetAsync(a.tile_counter, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
+    kern<<<dim3((unsigned)(sm_count * perSm)), BLOCK_THREADS, smem, st>>>(a);
+  } else {
+    auto kern = render_tiles_kernel<KIND, COUNT, SECONDARY>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 7u) / 8u);
+    kern<<<grid, BLOCK_THREADS, smem, st>>>(a);
+  }
+  return cudaGetLastError();
+}
+
+template <int KIND>
+static cudaError_t launch_render_k(const RenderArgs &a, int sched, int sm_count, cudaStream_t st) {
+  const bool secondary = a.frame.mode == RT_SHADE_LAMBERT && (a.frame.shadows || a.frame.reflections);
+  const bool count = a.counters != nullptr;
+  if (secondary) return count ? launch_render_t<KIND, true, true>(a, sched, sm_count, st)
+                              : launch_render_t<KIND, false, true>(a, sched, sm_count, st);
+  return count ? launch_render_t<KIND, true, false>(a, sched, sm_count, st)
+               : launch_render_t<KIND, false, false>(a, sched, sm_count, st);
+}
+
+cudaError_t launch_render(const RenderArgs &a, int sched, int sm_count, cudaStream_t st) {
+  if (a.frame.rows_here == 0 || a.frame.W == 0) return cudaSuccess;
+  switch (kind_of(a.scene)) {
+    case KIND_GRID: return launch_render_k<KIND_GRID>(a, sched, sm_count, st);
+    case KIND_OCTREE: return launch_render_k<KIND_OCTREE>(a, sched, sm_count, st);
+    case KIND_BVH: return launch_render_k<KIND_BVH>(a, sched, sm_count, st);
+    default: return launch_render_k<KIND_BRUTE>(a, sched, sm_count, st);
+  }
+}
+
+template <int KIND>
+static cudaError_t launch_rays_k(const RayArgs &a, cudaStream_t st) {
+  const size_t smem = (KIND == KIND_BRUTE) ? (size_t)a.scene.mesh.n_tris * sizeof(TriDev) : 0;
+  auto kern = rays_kernel<KIND>;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  kern<<<(a.n + BLOCK_THREADS - 1) / BLOCK_THREADS, BLOCK_THREADS, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rays(const RayArgs &a, cudaStream_t st) {
+  if (a.n == 0) return cudaSuccess;
+  switch (kind_of(a.scene)) {
+    case KIND_GRID: return launch_rays_k<KIND_GRID>(a, st);
+    case KIND_OCTREE: return launch_rays_k<KIND_OCTREE>(a, st);
+    case KIND_BVH: return launch_rays_k<KIND_BVH>(a, st);
+    default: return launch_rays_k<KIND_BRUTE>(a, st);
+  }
+}
+
+}  // namespace RT_NS
+}  // namespace rt

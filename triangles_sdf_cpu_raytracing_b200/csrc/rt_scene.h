@@ -1,0 +1,123 @@
+// Device-visible scene descriptors and launch parameters (plain structs shared by rt_api.cu and the kernels).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/rt_b200.h"
+
+namespace rt {
+
+// ---- dense SDF grid (replaces SDFGrid, grid_raytracing.hpp:10-21) ---------------------------------------
+// LINEAR: values[(x*sy + y)*sz + z], the reference's own order.
+// BRICKS: the grid is cut into 8x8x8-sample bricks (bx,by,bz), brick-major with the same x-major/z-fastest
+//         order inside a brick: a 2 KB brick = 16 lines of 128 B, so the 8 corners of a trilinear cell touch
+//         1-2 lines when they fall inside one brick instead of 4 far-apart lines.
+struct GridDev {
+  const float *values;
+  uint32_t sx, sy, sz;
+  uint32_t bricks;      // 0 linear, 1 bricked
+  uint32_t nby, nbz;    // bricks per axis (y, z) when bricked
+};
+
+// ---- SDF octree (replaces SDFOctree, octree_raytracing.hpp:8-47) ----------------------------------------
+// The 36-byte disk node is split at upload: `link[node]` holds the traversal word, `values[2*node..]` the 8
+// corner distances as two 16-byte-aligned float4 (only ever read for surface leaves).
+//   link == OCT_LEAF_CULLED : leaf that intersectLeaf rejects from its values alone (isEmpty
+//                             octree_raytracing.hpp:12-17, or all >= 1e-4 octree_raytracing.cpp:132-135)
+//   link == OCT_LEAF_SURFACE: leaf that must be marched
+//   otherwise               : childrenOffset of an inner node
+constexpr uint32_t OCT_LEAF_SURFACE = 0u;
+constexpr uint32_t OCT_LEAF_CULLED = 0xFFFFFFFFu;
+constexpr int OCT_MAX_DEPTH = 22;  // child boxes stay exactly representable
+struct OctreeDev {
+  const uint32_t *link;
+  const float4 *values;
+  uint32_t n_nodes;
+  uint32_t depth;
+};
+
+// ---- triangle mesh ------------------------------------------------------------------------------------
+// 8-wide BVH node: child boxes SoA as in Box8 (triangles_raytracing.hpp:10-17) followed by 8 child words.
+//   child == BVH_EMPTY           : unused lane (the reference leaves garbage there)
+//   child &  BVH_LEAF_BIT        : leaf: bits 0..26 first triangle, bits 27..30 triangle count - 1
+//   otherwise                    : index of an inner node
+// 224 bytes, 32-byte aligned: 14 x LDG.128 per visit.
+constexpr uint32_t BVH_EMPTY = 0xFFFFFFFFu;
+constexpr uint32_t BVH_LEAF_BIT = 0x80000000u;
+constexpr int BVH_STACK = 128;  // scene creation rejects trees that could need more
+struct alignas(32) BvhNode {
+  float lo[3][8];  // xMin[8], yMin[8], zMin[8]
+  float hi[3][8];  // xMax[8], yMax[8], zMax[8]
+  uint32_t child[8];
+};
+static_assert(sizeof(BvhNode) == 224, "BvhNode layout");
+
+// Leaf triangles pre-gathered in BVH order (removes the per-visit gather of triangles_raytracing.cpp:299-320):
+// v0.xyz | prim id, v1.xyz | 0, v2.xyz | 0, already divided by w (same IEEE division as :307-309).
+struct alignas(16) TriDev {
+  float4 v0, v1, v2;
+};
+
+struct MeshDev {
+  const BvhNode *nodes;
+  const TriDev *tris;
+  uint32_t n_nodes, n_tris;
+  uint32_t brute;  // 1: no BVH, all triangles are tested from shared memory
+};
+
+struct SceneDev {
+  int32_t kind;  // rt_scene_kind
+  GridDev grid;
+  OctreeDev oct;
+  MeshDev mesh;
+};
+
+// ---- per-launch parameters ------------------------------------------------------------------------------
+struct FrameDev {
+  float ray_pos[3];
+  float view_inv[16];
+  float proj_inv[16];
+  uint32_t W, H;
+  uint32_t band_rows, band_count, band_index;
+  uint32_t rows_here;  // number of memory rows this call renders
+  int32_t mode;
+  float light[3];
+  int32_t shadows, reflections, has_plane;
+  float plane_y;
+  float t_near, t_far;
+};
+
+struct RenderArgs {
+  SceneDev scene;
+  FrameDev frame;
+  uint32_t *color;
+  const float *t_in;
+  float *t_out;
+  uint32_t *prim;
+  unsigned long long *counters;  // rt_counters as 9 x u64, or null
+  uint32_t *tile_counter;        // persistent scheduling: next tile to hand out
+};
+
+struct RayArgs {
+  SceneDev scene;
+  const float *origins, *dirs;
+  uint32_t n;
+  float t_near, t_far;
+  int32_t has_plane;
+  float plane_y;
+  uint8_t *hit;
+  float *t;
+  float *normal;
+  uint32_t *prim;
+};
+
+// launchers, one set per arithmetic flavour (rt_kernels.cuh compiled twice)
+#define RT_DECLARE_LAUNCHERS(NS)                                                         \
+  namespace NS {                                                                         \
+  cudaError_t launch_render(const RenderArgs &a, int sched, int sm_count, cudaStream_t s); \
+  cudaError_t launch_rays(const RayArgs &a, cudaStream_t s);                             \
+  }
+RT_DECLARE_LAUNCHERS(exact)
+RT_DECLARE_LAUNCHERS(fast)
+
+}  // namespace rt

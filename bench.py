@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the primary-ray hot path on B200, next to the reference's CPU renderer.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--scene NAME] [--math exact|fast]
+
+A "step" is one frame: every primary ray of the workload goes through the CUDA path once (clear + render, and for
+N > 1 the gather of the screen-space tiles to rank 0).  The N=1 workload is BASELINE.json configs[1]: the
+stanford-bunny dense SDF grid (example_grid.grid, 65^3) sphere-traced at 1920x1080 with the viewer's start
+camera, ShadingMode::Normal, model only.  Prints ONE JSON line (see DESIGN.md "Measurement").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from tests import util  # noqa: E402  (fixtures only: scene arrays + the camera matrices the reference computed)
+
+WORKLOADS = {
+    # name: (scene fixture, golden case holding the camera matrices for this aspect ratio, W, H)
+    "grid65_1080p": ("example_grid", "example_grid|default|160x90", 1920, 1080),
+    "cube_512": ("cube", "cube|default|128x128", 512, 512),
+    "octree6_4k": ("sdf_6", "sdf_6|default|160x90", 3840, 2160),
+    "bunny_4k": ("stanford-bunny", "stanford-bunny|default|160x90", 3840, 2160),
+    "grid65_4k": ("example_grid", "example_grid|default|160x90", 3840, 2160),
+}
+HEADLINE = "grid65_1080p"
+METRIC = "Mrays/s primary rays"
+L2_FLUSH_BYTES = 256 << 20
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.06)
+            self.proc.terminate()
+            self.th.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def load_workload(name):
+    g = util.Golden()
+    scene_name, case_key, W, H = WORKLOADS[name]
+    c = g.case(case_key)
+    assert abs(W / H - c["W"] / c["H"]) < 1e-6
+    return g, scene_name, c, W, H
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's own CPU implementation of the path (oracle/_ref when it was compiled, else the C port),
+    all host threads, on the same workload.  Each step = a bounded band of rows of the frame."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    g, scene_name, c, W, H = load_workload(args.scene)
+    from oracle import ref_oracle as R
+    cores = os.cpu_count() or 1
+    if R.available(contract=True):
+        o = R.RefOracle(contract=True)  # GCC's default contraction = the reference's Release build
+        o.set_threads(cores)
+        a = g.scene_arrays(scene_name)
+        s = o.grid(a["values"]) if "values" in a else o.octree(a["nodes36"]) if "nodes36" in a else o.mesh(a["vpos4"], a["indices"])
+        cam = R.CamSpec()
+        kind = "reference"
+
+        def rows(y0, y1):
+            return s.render_rows(cam, W, H, y0, y1, proj_inv=c["projInv"])[2]
+    else:
+        from oracle import port_oracle as P
+        s = util.port_scene(g, scene_name)
+        kind = "port"
+
+        def rows(y0, y1):
+            t0 = time.perf_counter()
+            s.render(c["rayPos"], c["viewInv"], c["projInv"], W, H, rows=(y0, y1))
+            return (time.perf_counter() - t0) * 1e3
+    # size the per-step sample: a centred band of rows (the model is mid-screen) so that the run stays bounded
+    probe_rows = max(8, H // 16)
+    y0 = (H - probe_rows) // 2
+    ms_probe = rows(y0, y0 + probe_rows)
+    budget_ms = 90_000.0 / max(1, args.steps + args.warmup)
+    n_rows = int(min(H, max(8, probe_rows * budget_ms / max(ms_probe, 1e-3))))
+    y0 = (H - n_rows) // 2
+    for _ in range(args.warmup):
+        rows(y0, y0 + n_rows)
+    total = 0.0
+    for _ in range(args.steps):
+        total += rows(y0, y0 + n_rows)
+    ms = total / args.steps
+    value = n_rows * W / ms / 1e3
+    sample = f"rows {y0}..{y0 + n_rows} of {H} ({n_rows * W} rays per step), Renderer-equivalent row loop, OpenMP dynamic"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "reference scene file (fixture copy), viewer start camera",
+        "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal"},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ CUDA arm
+def cpu_baseline(g, scene_name, c, W, H):
+    """Rank 0, N=1: the reference's CPU path timed on this box's host cores on a bounded sample."""
+    from oracle import ref_oracle as R
+    cores = os.cpu_count() or 1
+    try:
+        if R.available(contract=True):
+            o = R.RefOracle(contract=True)
+            o.set_threads(cores)
+            a = g.scene_arrays(scene_name)
+            s = o.grid(a["values"]) if "values" in a else o.octree(a["nodes36"]) if "nodes36" in a else o.mesh(a["vpos4"], a["indices"])
+            best, each = s.render_timed(R.CamSpec(), W, H, frames=3, proj_inv=c["projInv"])
+            return {"value": W * H / best / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "reference",
+                    "sample": f"3 full {W}x{H} frames through the reference's Renderer::draw (best), scalar ISPC stand-in"}
+    except Exception as e:  # noqa: BLE001 - fall through to the port
+        sys.stderr.write(f"reference oracle unavailable ({e}); timing the C port\n")
+    s = util.port_scene(g, scene_name)
+    t0 = time.perf_counter()
+    s.render(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+    ms = (time.perf_counter() - t0) * 1e3
+    return {"value": W * H / ms / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "port",
+            "sample": f"1 full {W}x{H} frame through oracle/port_oracle.c (OpenMP)"}
+
+
+def oracle_frame(g, scene_name, c, W, H):
+    """The checker's frame for the timed workload (outside any timing). SDF scenes: the plain-C oracle. Meshes: the
+    reference's own code when oracle/_ref is present (it builds its BVH); the C oracle's brute force would need
+    rays x triangles tests and is only used for small meshes."""
+    a = g.scene_arrays(scene_name)
+    if "vpos4" not in a or a["indices"].size // 3 <= 64:
+        wc, wt, _, _ = util.port_scene(g, scene_name).render(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+        return wc, wt, "oracle/port_oracle.c"
+    from oracle import ref_oracle as R
+    if not R.available():
+        return None
+    o = R.RefOracle()
+    wc, wt, _ = o.mesh(a["vpos4"], a["indices"]).render(R.CamSpec(), W, H, proj_inv=c["projInv"])
+    return wc, wt, "oracle/_ref (reference C++, -ffp-contract=off)"
+
+
+def algorithmic_work(scene_kind, cnt, rays):
+    """algorithmic bytes and flops per frame from the live workload counters."""
+    S = cnt["grid_samples"] / rays
+    I, Lf, Ls = cnt["oct_inner"] / rays, cnt["oct_leaf"] / rays, cnt["oct_leaf_samples"] / rays
+    BI, BL, BT = cnt["bvh_inner"] / rays, cnt["bvh_leaf"] / rays, cnt["bvh_tris"] / rays
+    hit = cnt["hits"] / rays
+    if scene_kind == "grid":
+        b, f = 32 * S + 8, 150 + 60 * S
+    elif scene_kind == "octree":
+        b, f = 36 * (I + Lf) + 8, 107 + 300 * I + 70 * Lf + 73 * Ls + 130 * hit
+    else:
+        b, f = 204 * BI + 8 * BL + 60 * BT + 8, 107 + 254 * BI + 90 * BT
+    return b * rays, f * rays
+
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+
+    import triangles_sdf_cpu_raytracing_b200 as rt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rt.set_math_mode(rt.MATH_FAST if args.math == "fast" else rt.MATH_EXACT)
+    rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT}[args.sched])
+
+    g, scene_name, c, W, H = load_workload(args.scene)
+    scene = util.cuda_scene(g, scene_name)
+    kind = {0: "grid", 1: "octree", 2: "mesh"}[scene.kind]
+    band_rows = 32
+    bands = (band_rows, world, rank) if world > 1 else None
+    frame = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands)
+    px = W * H
+    color = torch.zeros(px, dtype=torch.int32, device=dev)
+    tbuf = torch.full((px,), float("inf"), dtype=torch.float32, device=dev)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream()
+    n_bands = (H + band_rows - 1) // band_rows
+    pad_rows = n_bands * band_rows
+
+    def gather_tiles():
+        """N > 1: every rank ships its interleaved row bands to rank 0 (NCCL send/recv over NVLink)."""
+        if world == 1:
+            return
+        cv = color.view(H, W)
+        tv = tbuf.view(H, W)
+        if rank == 0:
+            ops, stage = [], []
+            for r in range(1, world):
+                idx = [b for b in range(n_bands) if b % world == r]
+                nrows = sum(min(band_rows, H - b * band_rows) for b in idx)
+                sc = torch.empty((nrows, W), dtype=torch.int32, device=dev)
+                st = torch.empty((nrows, W), dtype=torch.float32, device=dev)
+                stage.append((idx, sc, st))
+                ops += [dist.P2POp(dist.irecv, sc, r), dist.P2POp(dist.irecv, st, r)]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            for idx, sc, st in stage:
+                o = 0
+                for b in idx:
+                    n = min(band_rows, H - b * band_rows)
+                    cv[b * band_rows:b * band_rows + n] = sc[o:o + n]
+                    tv[b * band_rows:b * band_rows + n] = st[o:o + n]
+                    o += n
+        else:
+            idx = [b for b in range(n_bands) if b % world == rank]
+            sc = torch.cat([cv[b * band_rows:min(H, (b + 1) * band_rows)] for b in idx])
+            st = torch.cat([tv[b * band_rows:min(H, (b + 1) * band_rows)] for b in idx])
+            for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, sc, 0), dist.P2POp(dist.isend, st, 0)]):
+                w.wait()
+
+    def step():
+        # FrameBuffer::clear (raytracing.hpp:16-19) + Renderer::draw
+        color.zero_()
+        tbuf.fill_(float("inf"))
+        scene.render_device(frame, color.data_ptr(), tbuf.data_ptr(), tbuf.data_ptr(), stream=stream.cuda_stream)
+        gather_tiles()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        barrier()
+        for a, b in ev:
+            flush.zero_()  # evict the scene and the framebuffer from L2 between timed iterations (untimed)
+            if world > 1:
+                dist.barrier()
+            a.record()
+            step()
+            b.record()
+        barrier()
+    ms_total = sum(a.elapsed_time(b) for a, b in ev)
+    if world > 1:
+        tt = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = px / ms_step / 1e3
+
+    # warm-L2 variant (frames back to back, as a viewer would issue them), kernel only
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        scene.render_device(frame, color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
+    b.record()
+    barrier()
+    kernel_ms_warm = a.elapsed_time(b) / args.steps
+    # kernel alone, cold L2 (the roofline's launch duration)
+    kev = []
+    for _ in range(min(args.steps, 50)):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        scene.render_device(frame, color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
+        b.record()
+        kev.append((a, b))
+    barrier()
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host framebuffer, copies inside the timed region)
+    e2e = None
+    if world == 1:
+        hc = torch.zeros(px, dtype=torch.int32).pin_memory()
+        ht = torch.full((px,), float("inf"), dtype=torch.float32).pin_memory()
+        import ctypes as C
+        from triangles_sdf_cpu_raytracing_b200 import _lib as L
+        dms, tms = C.c_float(), C.c_float()
+        n_e2e = max(5, min(args.steps, 30))
+        times = []
+        for i in range(n_e2e + 3):
+            hc.zero_()
+            ht.fill_(float("inf"))
+            t0 = time.perf_counter()
+            L.check(L.lib().rt_render_host(scene.handle, C.byref(frame), C.c_void_p(hc.data_ptr()),
+                                           C.c_void_p(ht.data_ptr()), None, C.byref(dms), C.byref(tms), None))
+            if i >= 3:
+                times.append((time.perf_counter() - t0) * 1e3)
+        e2e_ms = float(np.mean(times))
+        e2e = {"value": px / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": 8 * px, "d2h_bytes_per_step": 8 * px,
+               "api": "rt_render_host (pinned host framebuffer in/out)"}
+        # the frame that came back must be the reference's frame (checked against the oracle, outside any timing)
+        chk_c = hc.numpy().view(np.uint32).reshape(H, W).copy()
+        chk_t = ht.numpy().reshape(H, W).copy()
+
+    # ---- workload counters + roofline of the dominant (only) kernel
+    r = scene.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), want_counters=True)
+    cnt = r["counters"]
+    alg_bytes, alg_flops = algorithmic_work(kind, cnt, px)
+    hbm, peak_kind, sm_max = peaks()
+    clk = clocks.summary()
+    fp32_peak = 148 * 128 * 2 * (clk["sm_mhz"] or sm_max) * 1e6 / 1e12  # TFLOP/s at the clock seen under load
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                "traffic": None, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
+                "kernel_ms": kernel_ms, "kernel_ms_warm_l2": kernel_ms_warm,
+                "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_flops_per_launch": alg_flops,
+                "fp32": {"achieved_tflops": alg_flops / (kernel_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
+                         "frac": alg_flops / (kernel_ms * 1e-3) / 1e12 / fp32_peak},
+                "note": "scene fits in L2: the operative bounds are cached-gather latency and the FP32 pipe, see DESIGN.md"}
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "reference scene file (fixture copy), viewer start camera",
+        "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal",
+                   "math": args.math, "sched": args.sched, "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
+                   "partition": "whole frame" if world == 1 else f"{band_rows}-row bands interleaved over {world} GPUs, NCCL gather to rank 0"},
+        "clocks": clk, "gpu_launches": args.steps, "roofline": roofline,
+        "counters_per_ray": {k: v / px for k, v in cnt.items()},
+    }
+    if e2e is not None:
+        line["e2e"] = e2e
+        line["cpu_baseline"] = cpu_baseline(g, scene_name, c, W, H)
+        # correctness of what was timed: the e2e frame against the oracle port (bit-exact in exact mode)
+        want = oracle_frame(g, scene_name, c, W, H)
+        if want is not None:
+            wc, wt, who = want
+            d = util.compare_frames(chk_c, chk_t, wc, wt)
+            d["bit_identical"] = bool(util.same_bits(chk_t, wt) and np.array_equal(chk_c, wc))
+            d["checker"] = who
+            line["parity"] = d
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="cuda", choices=("cuda", "reference"))
+    ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
+    ap.add_argument("--math", default="exact", choices=("exact", "fast"))
+    ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -16,6 +16,25 @@ MESH_CASES = [c for c in G.cases if c.split("|")[0] in util.MESHES]
 _scene_cache = {}
 
 
+def assert_prim_mismatches_are_exact_ties(c, prim, want_prim, t, limit=0.02):
+    """Prim ids may differ from the reference's only where two triangles give the bit-identical closest t (shared
+    edges, duplicated geometry): the winner then depends on the visit order, i.e. on the tree.
+    Every such pixel is re-checked with the oracle's single-triangle test; they are counted and bounded."""
+    a = G.scene_arrays(c["scene"])
+    v = a["vpos4"].reshape(-1, 4)
+    idx = a["indices"].reshape(-1, 3)
+    ys, xs = np.nonzero(prim != want_prim)
+    assert ys.size <= limit * prim.size, f"{ys.size} prim-id mismatches"
+    for row, x in zip(ys, xs):
+        assert prim[row, x] != rt.PRIM_MISS and want_prim[row, x] != rt.PRIM_MISS
+        d = P.eye_ray(c["rayPos"], c["viewInv"], c["projInv"], prim.shape[1], prim.shape[0], int(x),
+                      int(prim.shape[0] - 1 - row))
+        tri = v[idx[prim[row, x]], :3] / v[idx[prim[row, x]], 3:4]
+        hit, tt, _ = P.triangle(c["rayPos"], d, tri.astype(np.float32))
+        assert hit and util.same_bits(tt, t[row, x]), f"pixel ({x},{row}): prim {prim[row, x]} is not a tie"
+    return ys.size
+
+
 def scene(name, **kw):
     key = (name, tuple(sorted(kw.items())))
     if key not in _scene_cache:
@@ -71,11 +90,12 @@ def test_mesh_scenes_vs_reference(key, accel):
     r = s.render(_frame(c), want_prim=True)
     # closest hit does not depend on the tree: depth and colour are bit-identical, prim ids may differ on exact ties
     assert util.same_bits(r["t"], c["t"]), f"{key}: depth differs on {(util.bits(r['t']) != util.bits(c['t'])).sum()} px"
-    assert np.array_equal(r["color"], c["color_normal"])
-    ties = r["prim"] != c["prim"]
-    assert ties.sum() <= max(2, 0.002 * ties.size), f"{key}: {ties.sum()} prim-id mismatches"
+    assert_prim_mismatches_are_exact_ties(c, r["prim"], c["prim"], c["t"])
+    same = r["prim"] == c["prim"]  # on a tie between two triangles the normal (colour) is the other triangle's
+    assert np.array_equal(r["color"][same], c["color_normal"][same])
+    assert util.rgb_max_diff(r["color"][~same] >> 24, c["color_normal"][~same] >> 24) == 0  # alpha: hit everywhere
     r = s.render(_frame(c, mode=rt.SHADE_LAMBERT))
-    assert np.array_equal(r["color"], c["color_lambert"])
+    assert np.array_equal(r["color"][same], c["color_lambert"][same])
 
 
 def test_reference_built_bvh_is_traversed_identically():
@@ -124,7 +144,8 @@ def test_larger_frames_vs_c_oracle(name, W, H):
         assert cn["oct_inner"] == want_cnt["octInner"] and cn["oct_leaf"] == want_cnt["octLeaf"]
         assert cn["oct_leaf_samples"] == want_cnt["octLeafSdf"]
     else:
-        assert (r["prim"] != want_p).sum() <= max(2, 0.002 * W * H)
+        cc = dict(c, W=W, H=H)
+        assert_prim_mismatches_are_exact_ties(cc, r["prim"], want_p, want_t)
 
 
 @pytest.mark.parametrize("key", [c for c in G.cases if "|default|" in c or "|orbit5|" in c])

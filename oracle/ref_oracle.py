@@ -47,6 +47,26 @@ class CamSpec:
         return r
 
 
+import contextlib
+import sys
+
+
+@contextlib.contextmanager
+def quiet_stdout():
+    """BVHBuilder::perform prints its build time to std::cout (triangles_raytracing.cpp:255-257); keep it out of
+    the caller's stdout (bench.py prints exactly one JSON line there)."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    try:
+        os.dup2(devnull, 1)
+        yield
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+        os.close(devnull)
+
+
 def _fp(a):
     return a.ctypes.data_as(C.POINTER(C.c_float))
 
@@ -147,10 +167,13 @@ class RefOracle:
     def mesh(self, vpos4: np.ndarray, indices: np.ndarray, scale: bool = False) -> "RefSceneHandle":
         v = np.ascontiguousarray(vpos4, dtype=np.float32).reshape(-1, 4)
         i = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
-        return RefSceneHandle(self, self.L.ref_scene_mesh(_fp(v), v.shape[0], _up(i), i.size, int(scale)))
+        with quiet_stdout():
+            h = self.L.ref_scene_mesh(_fp(v), v.shape[0], _up(i), i.size, int(scale))
+        return RefSceneHandle(self, h)
 
     def mesh_obj(self, path: str, scale: bool = True) -> "RefSceneHandle":
-        h = self.L.ref_scene_mesh_obj(path.encode(), int(scale))
+        with quiet_stdout():
+            h = self.L.ref_scene_mesh_obj(path.encode(), int(scale))
         if not h:
             raise RuntimeError(f"reference could not load {path}")
         return RefSceneHandle(self, h)

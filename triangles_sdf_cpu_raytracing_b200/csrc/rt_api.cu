@@ -165,7 +165,9 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   if (!values) return fail(RT_ERR_INVALID, "grid values pointer is null");
   // SDFGrid::sdf maps [-1,1] to [0,size-1] (grid_raytracing.cpp:8-11): every axis needs two samples
   if (sx < 2 || sy < 2 || sz < 2) return fail(RT_ERR_INVALID, "grid needs at least 2 samples per axis");
-  if ((uint64_t)sx * sy * sz >= (1ull << 32)) return fail(RT_ERR_INVALID, "grid too large (cell index must fit 32 bits)");
+  // element offsets are 32-bit on the device, also for the brick-padded copy
+  if ((uint64_t)((sx + 7) & ~7u) * ((sy + 7) & ~7u) * ((sz + 7) & ~7u) >= (1ull << 32))
+    return fail(RT_ERR_INVALID, "grid too large (element offsets must fit 32 bits)");
   if (layout < RT_GRID_AUTO || layout > RT_GRID_BRICKS) return fail(RT_ERR_INVALID, "unknown grid layout");
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
@@ -174,6 +176,7 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   s->dev.kind = RT_SCENE_GRID;
   GridDev &g = s->dev.grid;
   g.sx = sx; g.sy = sy; g.sz = sz;
+  g.fx = (float)(sx - 1); g.fy = (float)(sy - 1); g.fz = (float)(sz - 1);
   const size_t n = (size_t)sx * sy * sz;
   if (layout == RT_GRID_AUTO) layout = RT_GRID_LINEAR;  // chosen by measurement, DESIGN.md "grid layout"
   if (layout == RT_GRID_BRICKS) {
@@ -187,10 +190,10 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
           b[(br << 9) + (((x & 7u) << 6) | ((y & 7u) << 3) | (z & 7u))] = src[z];
         }
       }
-    g.bricks = 1; g.nby = nby; g.nbz = nbz;
+    g.bricks = 1; g.stride_x = nby * nbz * 512u; g.stride_y = nbz * 512u;
     rc = upload(s, b.data(), b.size(), &g.values);
   } else {
-    g.bricks = 0; g.nby = g.nbz = 0;
+    g.bricks = 0; g.stride_x = sy * sz; g.stride_y = sz;
     rc = upload(s, values, n, &g.values);
   }
   if (rc == RT_OK) rc = scene_finish(s, out);

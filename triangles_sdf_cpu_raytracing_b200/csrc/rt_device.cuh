@@ -142,34 +142,46 @@ __device__ __forceinline__ V3 ld3(const float4 &v) { return mk3(v.x, v.y, v.z); 
 // =============================================================================================================
 // Dense SDF grid (grid_raytracing.cpp)
 // =============================================================================================================
-__device__ __forceinline__ float grid_at(const GridDev &g, uint32_t x, uint32_t y, uint32_t z) {
-  if (g.bricks) {
-    // brick (x>>3, y>>3, z>>3), 512 floats per brick, same x-major / z-fastest order inside
-    size_t b = ((size_t)(x >> 3) * g.nby + (y >> 3)) * g.nbz + (z >> 3);
-    return __ldg(g.values + (b << 9) + (((x & 7u) << 6) | ((y & 7u) << 3) | (z & 7u)));
-  }
-  return __ldg(g.values + ((size_t)x * g.sy + y) * g.sz + z);  // grid_raytracing.hpp:13-15
+// Offsets of sample coordinate c along one axis; the element index is offx(x) + offy(y) + offz(z).
+// LINEAR: (x*sy + y)*sz + z (grid_raytracing.hpp:13-15).  BRICKS: 8x8x8 bricks of 512 floats, brick-major.
+template <bool BRICKS>
+__device__ __forceinline__ uint32_t grid_offx(const GridDev &g, uint32_t x) {
+  return BRICKS ? (x >> 3) * g.stride_x + ((x & 7u) << 6) : x * g.stride_x;
+}
+template <bool BRICKS>
+__device__ __forceinline__ uint32_t grid_offy(const GridDev &g, uint32_t y) {
+  return BRICKS ? (y >> 3) * g.stride_y + ((y & 7u) << 3) : y * g.stride_y;
+}
+template <bool BRICKS>
+__device__ __forceinline__ uint32_t grid_offz(uint32_t z) {
+  return BRICKS ? ((z >> 3) << 9) + (z & 7u) : z;
 }
 
-// SDFGrid::sdf(float3), grid_raytracing.cpp:7-62; cell = linear index of corner c0 (the grid's "prim id")
-template <bool COUNT>
+// SDFGrid::sdf(float3), grid_raytracing.cpp:7-62; cell = (c0x, c0y, c0z) packed by the caller when it wants the
+// grid's "prim id".  ceil(p) is evaluated as floor(p) + (p != floor(p)), the same value for 0 <= p < 2^23.
+template <bool BRICKS, bool COUNT>
 __device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell, Counters &cnt) {
   if (COUNT) cnt.grid_samples++;
   p.x = (p.x + 1.0f) / 2.0f; p.y = (p.y + 1.0f) / 2.0f; p.z = (p.z + 1.0f) / 2.0f;
-  p.x *= (float)(g.sx - 1); p.y *= (float)(g.sy - 1); p.z *= (float)(g.sz - 1);
-  float c0fx = floorf(p.x), c0fy = floorf(p.y), c0fz = floorf(p.z);
-  float c1fx = ceilf(p.x), c1fy = ceilf(p.y), c1fz = ceilf(p.z);
-  uint32_t c0x = (uint32_t)c0fx, c0y = (uint32_t)c0fy, c0z = (uint32_t)c0fz;
-  uint32_t c1x = (uint32_t)c1fx, c1y = (uint32_t)c1fy, c1z = (uint32_t)c1fz;
+  p.x *= g.fx; p.y *= g.fy; p.z *= g.fz;  // (float)(size - 1)
+  const float c0fx = floorf(p.x), c0fy = floorf(p.y), c0fz = floorf(p.z);
+  const uint32_t c0x = (uint32_t)c0fx, c0y = (uint32_t)c0fy, c0z = (uint32_t)c0fz;
+  const bool ix = p.x != c0fx, iy = p.y != c0fy, iz = p.z != c0fz;  // c1 != c0 on that axis
+  const float c1fx = ix ? c0fx + 1.0f : c0fx, c1fy = iy ? c0fy + 1.0f : c0fy, c1fz = iz ? c0fz + 1.0f : c0fz;
   float px = p.x - c0fx, py = p.y - c0fy, pz = p.z - c0fz;  // p_c0f
   float qx = c1fx - p.x, qy = c1fy - p.y, qz = c1fz - p.z;  // c1f_p
-  if (c1x == c0x) { px = 1.0f; qx = 0.0f; }                 // :25-38
-  if (c1y == c0y) { py = 1.0f; qy = 0.0f; }
-  if (c1z == c0z) { pz = 1.0f; qz = 0.0f; }
-  float v0 = grid_at(g, c0x, c0y, c0z), v1 = grid_at(g, c0x, c0y, c1z);
-  float v2 = grid_at(g, c0x, c1y, c0z), v3 = grid_at(g, c0x, c1y, c1z);
-  float v4 = grid_at(g, c1x, c0y, c0z), v5 = grid_at(g, c1x, c0y, c1z);
-  float v6 = grid_at(g, c1x, c1y, c0z), v7 = grid_at(g, c1x, c1y, c1z);
+  if (!ix) { px = 1.0f; qx = 0.0f; }                        // :25-38
+  if (!iy) { py = 1.0f; qy = 0.0f; }
+  if (!iz) { pz = 1.0f; qz = 0.0f; }
+  const uint32_t x0 = grid_offx<BRICKS>(g, c0x), x1 = ix ? grid_offx<BRICKS>(g, c0x + 1u) : x0;
+  const uint32_t y0 = grid_offy<BRICKS>(g, c0y), y1 = iy ? grid_offy<BRICKS>(g, c0y + 1u) : y0;
+  const uint32_t z0 = grid_offz<BRICKS>(c0z), z1 = iz ? grid_offz<BRICKS>(c0z + 1u) : z0;
+  const float *v = g.values;
+  const uint32_t a00 = x0 + y0, a01 = x0 + y1, a10 = x1 + y0, a11 = x1 + y1;
+  const float v0 = __ldg(v + (a00 + z0)), v1 = __ldg(v + (a00 + z1));
+  const float v2 = __ldg(v + (a01 + z0)), v3 = __ldg(v + (a01 + z1));
+  const float v4 = __ldg(v + (a10 + z0)), v5 = __ldg(v + (a10 + z1));
+  const float v6 = __ldg(v + (a11 + z0)), v7 = __ldg(v + (a11 + z1));
   float res = 0.0f;
   res += v0 * qx * qy * qz;
   res += v1 * qx * qy * pz;
@@ -179,26 +191,28 @@ __device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell
   res += v5 * px * qy * pz;
   res += v6 * px * py * qz;
   res += v7 * px * py * pz;
-  cell = (uint32_t)(((size_t)c0x * g.sy + c0y) * g.sz + c0z);
+  cell = (c0x * g.sy + c0y) * g.sz + c0z;
   return res;
 }
 
 // SDFGrid::normal, grid_raytracing.cpp:64-89: clamped +-1e-3 differences, not scaled, then normalize
-template <bool COUNT>
+template <bool BRICKS, bool COUNT>
 __device__ __forceinline__ V3 grid_normal(const GridDev &g, V3 p, Counters &cnt) {
   const float E = 1e-3f;
   float xL = (p.x - E >= -1.0f) ? p.x - E : p.x, xR = (p.x + E <= 1.0f) ? p.x + E : p.x;
   float yL = (p.y - E >= -1.0f) ? p.y - E : p.y, yR = (p.y + E <= 1.0f) ? p.y + E : p.y;
   float zL = (p.z - E >= -1.0f) ? p.z - E : p.z, zR = (p.z + E <= 1.0f) ? p.z + E : p.z;
   uint32_t c;
-  float dx = grid_sdf<COUNT>(g, mk3(xR, p.y, p.z), c, cnt) - grid_sdf<COUNT>(g, mk3(xL, p.y, p.z), c, cnt);
-  float dy = grid_sdf<COUNT>(g, mk3(p.x, yR, p.z), c, cnt) - grid_sdf<COUNT>(g, mk3(p.x, yL, p.z), c, cnt);
-  float dz = grid_sdf<COUNT>(g, mk3(p.x, p.y, zR), c, cnt) - grid_sdf<COUNT>(g, mk3(p.x, p.y, zL), c, cnt);
+  float dx = grid_sdf<BRICKS, COUNT>(g, mk3(xR, p.y, p.z), c, cnt) - grid_sdf<BRICKS, COUNT>(g, mk3(xL, p.y, p.z), c, cnt);
+  float dy = grid_sdf<BRICKS, COUNT>(g, mk3(p.x, yR, p.z), c, cnt) - grid_sdf<BRICKS, COUNT>(g, mk3(p.x, yL, p.z), c, cnt);
+  float dz = grid_sdf<BRICKS, COUNT>(g, mk3(p.x, p.y, zR), c, cnt) - grid_sdf<BRICKS, COUNT>(g, mk3(p.x, p.y, zL), c, cnt);
   return lm_normalize(mk3(dx, dy, dz));
 }
 
-// SDFGrid::intersect, grid_raytracing.cpp:93-125
-template <bool COUNT>
+// SDFGrid::intersect, grid_raytracing.cpp:93-125.  The march loop only marches; the hit's normal (6 more samples)
+// is evaluated after the loop so that all lanes of the warp that hit do it together instead of one by one at
+// the iteration each of them happens to hit.
+template <bool BRICKS, bool COUNT>
 __device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
   V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
@@ -211,17 +225,17 @@ __device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, floa
   p.x = std_min(p.x, 1.0f); p.y = std_min(p.y, 1.0f); p.z = std_min(p.z, 1.0f);
   while (p.x <= 1.0f && p.y <= 1.0f && p.z <= 1.0f && p.x >= -1.0f && p.y >= -1.0f && p.z >= -1.0f) {
     uint32_t cell;
-    float sd = grid_sdf<COUNT>(g, p, cell, cnt);
+    float sd = grid_sdf<BRICKS, COUNT>(g, p, cell, cnt);
     if (sd < 1e-3f) {
       r.hitten = true;
       r.t = t + sd;
-      r.normal = grid_normal<COUNT>(g, p, cnt);
       r.prim = cell;
       break;
     }
     t += sd;
     p = along(o, d, t);
   }
+  if (r.hitten) r.normal = grid_normal<BRICKS, COUNT>(g, p, cnt);
   return r;
 }
 
@@ -274,10 +288,11 @@ __device__ __forceinline__ V3 oct_node_normal(const float (&v)[8], V3 bmin, floa
   return lm_normalize(mk3(dfdx, dfdy, dfdz));
 }
 
-// SDFOctree::intersectLeaf, octree_raytracing.cpp:122-164, for a leaf that survived the value culls
+// SDFOctree::intersectLeaf, octree_raytracing.cpp:122-164, for a leaf that survived the value culls.
+// On a hit the sample point is returned in `pHit`; the caller evaluates the normal once the traversal is over.
 template <bool COUNT>
 __device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 bmin, float ext, V3 o, V3 d, V3 inv,
-                                         float tNear, float tFar, Hit &r, Counters &cnt) {
+                                         float tNear, float tFar, Hit &r, V3 &pHit, Counters &cnt) {
   V3 bmax = mk3(bmin.x + ext, bmin.y + ext, bmin.z + ext);
   float t1, t2;
   bbox_intersection(bmin, bmax, o, inv, tNear, tFar, t1, t2);
@@ -295,8 +310,8 @@ __device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 
     if (sd < 1e-4f) {
       r.hitten = true;
       r.t = t + sd;
-      r.normal = oct_node_normal(v, bmin, invExt, p);
       r.prim = node;
+      pHit = p;
       return true;
     }
     t += sd;
@@ -320,6 +335,8 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   int level = 0;                      // level of `node`
   uint32_t node = 0, ix = 0, iy = 0, iz = 0;
   float ext = 2.0f;                   // edge of the current node's box
+  V3 hitMin = mk3(0.0f, 0.0f, 0.0f), pHit = hitMin;
+  float hitExt = 0.0f;
   for (;;) {
     // ---- visit `node` at (level, ix, iy, iz)
     const uint32_t link = __ldg(oc.link + node);
@@ -327,17 +344,37 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     bool descend = false;
     if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
       if (COUNT) cnt.oct_leaf++;
-      if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, node, bmin, ext, o, d, inv, tNear, tFar, r, cnt)) return r;
+      if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, node, bmin, ext, o, d, inv, tNear, tFar, r, pHit, cnt)) {
+        hitMin = bmin;
+        hitExt = ext;
+        break;
+      }
     } else {
       if (COUNT) cnt.oct_inner++;
+      // The 8 child boxes of divide_box_8 only have three distinct planes per axis (min, centre, max: centre + half
+      // is max exactly), so the 48 plane distances of intersect_box_8 are 9 distinct values and the per-axis
+      // min/max pairs 12: same operations on the same operands as ray_pack.ispc:255-263, evaluated once.
       const float h = ext * 0.5f;
-      const V3 c = mk3(bmin.x + h, bmin.y + h, bmin.z + h);  // (min+max)/2, exact
+      const float pl[3][3] = {{bmin.x, bmin.x + h, bmin.x + ext}, {bmin.y, bmin.y + h, bmin.y + ext},
+                              {bmin.z, bmin.z + h, bmin.z + ext}};
+      const float oo[3] = {o.x, o.y, o.z}, ii[3] = {inv.x, inv.y, inv.z};
+      float mn[3][2], mx[3][2];
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const float t0 = (pl[a][0] - oo[a]) * ii[a], t1 = (pl[a][1] - oo[a]) * ii[a], t2 = (pl[a][2] - oo[a]) * ii[a];
+        mn[a][0] = ispc_min(t0, t1); mx[a][0] = ispc_max(t0, t1);
+        mn[a][1] = ispc_min(t1, t2); mx[a][1] = ispc_max(t1, t2);
+      }
       float ts[8];
       uint32_t ch[8];
 #pragma unroll
       for (int id = 0; id < 8; ++id) {
-        const float mx = (id & 4) ? c.x : bmin.x, my = (id & 2) ? c.y : bmin.y, mz = (id & 1) ? c.z : bmin.z;
-        ts[id] = slab_lane(mx, my, mz, mx + h, my + h, mz + h, o, inv, tNear, tFar);
+        const int cx = (id >> 2) & 1, cy = (id >> 1) & 1, cz = id & 1;
+        float tMin = ispc_max(mn[0][cx], ispc_max(mn[1][cy], mn[2][cz]));
+        float tMax = ispc_min(mx[0][cx], ispc_min(mx[1][cy], mx[2][cz]));
+        tMin = ispc_max(tMin, tNear);
+        tMax = ispc_min(tMax, tFar);
+        ts[id] = (tMax < 0 || tMin > tMax) ? -1.0f : tMin;
         ch[id] = id;
       }
       sort8(ts, ch);
@@ -353,13 +390,15 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     }
     if (!descend) {
       // ---- climb to the deepest ancestor that still has pending children
+      bool done = false;
       for (;;) {
-        if (level == 0) return r;
+        if (level == 0) { done = true; break; }
         --level;
         ix >>= 1; iy >>= 1; iz >>= 1;
         ext *= 2.0f;
         if (pend[level]) break;
       }
+      if (done) break;
     }
     const uint32_t w = pend[level];
     const uint32_t id = w & 7u;
@@ -371,6 +410,13 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     ext *= 0.5f;
     ++level;
   }
+  if (r.hitten) {
+    // the hit leaf's normal, evaluated by all lanes that hit together (values are an L1 hit)
+    const float4 a = __ldg(oc.values + 2 * (size_t)r.prim), b = __ldg(oc.values + 2 * (size_t)r.prim + 1);
+    const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    r.normal = oct_node_normal(v, hitMin, 1.0f / hitExt, pHit);
+  }
+  return r;
 }
 
 // =============================================================================================================

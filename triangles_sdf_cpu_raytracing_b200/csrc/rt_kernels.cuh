@@ -12,7 +12,7 @@ namespace RT_NS {
 
 #include "rt_device.cuh"
 
-constexpr int KIND_GRID = 0, KIND_OCTREE = 1, KIND_BVH = 2, KIND_BRUTE = 3;
+constexpr int KIND_GRID = 0, KIND_OCTREE = 1, KIND_BVH = 2, KIND_BRUTE = 3, KIND_GRID_BRICKS = 4;
 constexpr int BLOCK_THREADS = 256;
 // a warp owns an 8x4 pixel tile; a 256-thread block owns 32x8 pixels (4 warps across, 2 down)
 constexpr int TILE_W = 8, TILE_H = 4;
@@ -22,7 +22,8 @@ template <int KIND, bool COUNT>
 __device__ __forceinline__ Hit model_intersect(const SceneDev &s, const float4 *smemTris, V3 o, V3 d, float tNear,
                                                float tFar, Counters &cnt) {
   if (COUNT) cnt.rays++;
-  if (KIND == KIND_GRID) return grid_intersect<COUNT>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_GRID) return grid_intersect<false, COUNT>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_GRID_BRICKS) return grid_intersect<true, COUNT>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_OCTREE) return oct_intersect<COUNT>(s.oct, o, d, tNear, tFar, cnt);
   if (KIND == KIND_BVH) return bvh_intersect<COUNT>(s.mesh, o, d, tNear, tFar, cnt);
   return brute_intersect<COUNT>(smemTris, s.mesh.n_tris, o, d, cnt);
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS) rays_kernel(const __grid_consta
 
 // ---- launchers ------------------------------------------------------------------------------------------------
 static inline int kind_of(const SceneDev &s) {
-  if (s.kind == RT_SCENE_GRID) return KIND_GRID;
+  if (s.kind == RT_SCENE_GRID) return s.grid.bricks ? KIND_GRID_BRICKS : KIND_GRID;
   if (s.kind == RT_SCENE_OCTREE) return KIND_OCTREE;
   return s.mesh.brute ? KIND_BRUTE : KIND_BVH;
 }
@@ -312,6 +313,7 @@ cudaError_t launch_render(const RenderArgs &a, int sched, int sm_count, cudaStre
   if (a.frame.rows_here == 0 || a.frame.W == 0) return cudaSuccess;
   switch (kind_of(a.scene)) {
     case KIND_GRID: return launch_render_k<KIND_GRID>(a, sched, sm_count, st);
+    case KIND_GRID_BRICKS: return launch_render_k<KIND_GRID_BRICKS>(a, sched, sm_count, st);
     case KIND_OCTREE: return launch_render_k<KIND_OCTREE>(a, sched, sm_count, st);
     case KIND_BVH: return launch_render_k<KIND_BVH>(a, sched, sm_count, st);
     default: return launch_render_k<KIND_BRUTE>(a, sched, sm_count, st);
@@ -331,6 +333,7 @@ cudaError_t launch_rays(const RayArgs &a, cudaStream_t st) {
   if (a.n == 0) return cudaSuccess;
   switch (kind_of(a.scene)) {
     case KIND_GRID: return launch_rays_k<KIND_GRID>(a, st);
+    case KIND_GRID_BRICKS: return launch_rays_k<KIND_GRID_BRICKS>(a, st);
     case KIND_OCTREE: return launch_rays_k<KIND_OCTREE>(a, st);
     case KIND_BVH: return launch_rays_k<KIND_BVH>(a, st);
     default: return launch_rays_k<KIND_BRUTE>(a, st);

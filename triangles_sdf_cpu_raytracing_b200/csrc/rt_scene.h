@@ -15,8 +15,9 @@ namespace rt {
 struct GridDev {
   const float *values;
   uint32_t sx, sy, sz;
-  uint32_t bricks;      // 0 linear, 1 bricked
-  uint32_t nby, nbz;    // bricks per axis (y, z) when bricked
+  uint32_t bricks;              // 0 linear, 1 bricked
+  uint32_t stride_x, stride_y;  // linear: sy*sz, sz;  bricked: nby*nbz*512, nbz*512 (elements)
+  float fx, fy, fz;             // (float)(size - 1), grid_raytracing.cpp:9-11
 };
 
 // ---- SDF octree (replaces SDFOctree, octree_raytracing.hpp:8-47) ----------------------------------------

@@ -88,16 +88,25 @@ __device__ __forceinline__ void bbox_intersection(V3 bmin, V3 bmax, V3 o, V3 inv
 }
 
 // ---- ispc::intersect_box_8, one lane (ray_pack.ispc:241-273) ---------------------------------------------
+// NANFREE: the caller knows all three 1/dir are finite, so no plane distance can be NaN (NaN needs 0 * inf) and
+// ISPC's select-form min/max (second operand on NaN) equals the hardware FMNMX up to the sign of a zero, which
+// nothing downstream observes (entry distances are only compared with each other, with hit.t and with 0).
+template <bool NANFREE>
+__device__ __forceinline__ float mn2(float a, float b) { return NANFREE ? fminf(a, b) : ispc_min(a, b); }
+template <bool NANFREE>
+__device__ __forceinline__ float mx2(float a, float b) { return NANFREE ? fmaxf(a, b) : ispc_max(a, b); }
+
+template <bool NANFREE>
 __device__ __forceinline__ float slab_lane(float xMin, float yMin, float zMin, float xMax, float yMax, float zMax, V3 o,
                                            V3 inv, float tNear, float tFar) {
   float t1x = (xMin - o.x) * inv.x, t1y = (yMin - o.y) * inv.y, t1z = (zMin - o.z) * inv.z;
   float t2x = (xMax - o.x) * inv.x, t2y = (yMax - o.y) * inv.y, t2z = (zMax - o.z) * inv.z;
-  float mnx = ispc_min(t1x, t2x), mny = ispc_min(t1y, t2y), mnz = ispc_min(t1z, t2z);
-  float mxx = ispc_max(t1x, t2x), mxy = ispc_max(t1y, t2y), mxz = ispc_max(t1z, t2z);
-  float tMin = ispc_max(mnx, ispc_max(mny, mnz));
-  float tMax = ispc_min(mxx, ispc_min(mxy, mxz));
-  tMin = ispc_max(tMin, tNear);
-  tMax = ispc_min(tMax, tFar);
+  float mnx = mn2<NANFREE>(t1x, t2x), mny = mn2<NANFREE>(t1y, t2y), mnz = mn2<NANFREE>(t1z, t2z);
+  float mxx = mx2<NANFREE>(t1x, t2x), mxy = mx2<NANFREE>(t1y, t2y), mxz = mx2<NANFREE>(t1z, t2z);
+  float tMin = mx2<NANFREE>(mnx, mx2<NANFREE>(mny, mnz));
+  float tMax = mn2<NANFREE>(mxx, mn2<NANFREE>(mxy, mxz));
+  tMin = mx2<NANFREE>(tMin, tNear);
+  tMax = mn2<NANFREE>(tMax, tFar);
   if (tMax < 0 || tMin > tMax) return -1.0f;
   return tMin;
 }
@@ -320,6 +329,39 @@ __device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 
   return false;
 }
 
+// divide_box_8 + intersect_box_8 for one inner node (ray_pack.ispc:220-273): entry distance of the ray into each of
+// the 8 child boxes, -1 on a miss.  The 8 child boxes only have three distinct planes per axis (min, centre, max:
+// centre + half is max exactly), so the 48 plane distances are 9 distinct values and the per-axis min/max pairs 12:
+// the same operations on the same operands as ray_pack.ispc:255-263, each evaluated once.
+// NANFREE: all three 1/dir are finite, so no plane distance can be NaN (NaN needs 0 * inf) and the select-form
+// min/max of ISPC (second operand on NaN) equals the hardware FMNMX up to the sign of a zero, which nothing
+// downstream can observe (the distances are only compared with each other and with 0).
+template <bool NANFREE>
+__device__ __forceinline__ void oct_child_entries(V3 bmin, float ext, V3 o, V3 inv, float tNear, float tFar,
+                                                  float (&ts)[8], uint32_t (&ch)[8]) {
+  const float h = ext * 0.5f;
+  const float pl[3][3] = {{bmin.x, bmin.x + h, bmin.x + ext}, {bmin.y, bmin.y + h, bmin.y + ext},
+                          {bmin.z, bmin.z + h, bmin.z + ext}};
+  const float oo[3] = {o.x, o.y, o.z}, ii[3] = {inv.x, inv.y, inv.z};
+  float mn[3][2], mx[3][2];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float t0 = (pl[a][0] - oo[a]) * ii[a], t1 = (pl[a][1] - oo[a]) * ii[a], t2 = (pl[a][2] - oo[a]) * ii[a];
+    mn[a][0] = mn2<NANFREE>(t0, t1); mx[a][0] = mx2<NANFREE>(t0, t1);
+    mn[a][1] = mn2<NANFREE>(t1, t2); mx[a][1] = mx2<NANFREE>(t1, t2);
+  }
+#pragma unroll
+  for (int id = 0; id < 8; ++id) {
+    const int cx = (id >> 2) & 1, cy = (id >> 1) & 1, cz = id & 1;
+    float tMin = mx2<NANFREE>(mn[0][cx], mx2<NANFREE>(mn[1][cy], mn[2][cz]));
+    float tMax = mn2<NANFREE>(mx[0][cx], mn2<NANFREE>(mx[1][cy], mx[2][cz]));
+    tMin = mx2<NANFREE>(tMin, tNear);
+    tMax = mn2<NANFREE>(tMax, tFar);
+    ts[id] = (tMax < 0 || tMin > tMax) ? -1.0f : tMin;
+    ch[id] = id;
+  }
+}
+
 // SDFOctree::intersectNode, octree_raytracing.cpp:166-202, as an explicit-stack ordered descent.
 // The reference recursion returns as soon as ANY leaf reports a hit (the first hitting child ends every
 // enclosing loop, :188-197), so `hit.t > t` is never evaluated with a hit in hand: the visit rule is just
@@ -330,6 +372,7 @@ template <bool COUNT>
 __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
   const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  const bool finiteInv = isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z);
   uint32_t pend[OCT_MAX_DEPTH + 1];   // pending children of the node at each level
   uint32_t base[OCT_MAX_DEPTH + 1];   // its childrenOffset
   int level = 0;                      // level of `node`
@@ -351,32 +394,10 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
       }
     } else {
       if (COUNT) cnt.oct_inner++;
-      // The 8 child boxes of divide_box_8 only have three distinct planes per axis (min, centre, max: centre + half
-      // is max exactly), so the 48 plane distances of intersect_box_8 are 9 distinct values and the per-axis
-      // min/max pairs 12: same operations on the same operands as ray_pack.ispc:255-263, evaluated once.
-      const float h = ext * 0.5f;
-      const float pl[3][3] = {{bmin.x, bmin.x + h, bmin.x + ext}, {bmin.y, bmin.y + h, bmin.y + ext},
-                              {bmin.z, bmin.z + h, bmin.z + ext}};
-      const float oo[3] = {o.x, o.y, o.z}, ii[3] = {inv.x, inv.y, inv.z};
-      float mn[3][2], mx[3][2];
-#pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        const float t0 = (pl[a][0] - oo[a]) * ii[a], t1 = (pl[a][1] - oo[a]) * ii[a], t2 = (pl[a][2] - oo[a]) * ii[a];
-        mn[a][0] = ispc_min(t0, t1); mx[a][0] = ispc_max(t0, t1);
-        mn[a][1] = ispc_min(t1, t2); mx[a][1] = ispc_max(t1, t2);
-      }
       float ts[8];
       uint32_t ch[8];
-#pragma unroll
-      for (int id = 0; id < 8; ++id) {
-        const int cx = (id >> 2) & 1, cy = (id >> 1) & 1, cz = id & 1;
-        float tMin = ispc_max(mn[0][cx], ispc_max(mn[1][cy], mn[2][cz]));
-        float tMax = ispc_min(mx[0][cx], ispc_min(mx[1][cy], mx[2][cz]));
-        tMin = ispc_max(tMin, tNear);
-        tMax = ispc_min(tMax, tFar);
-        ts[id] = (tMax < 0 || tMin > tMax) ? -1.0f : tMin;
-        ch[id] = id;
-      }
+      if (finiteInv) oct_child_entries<true>(bmin, ext, o, inv, tNear, tFar, ts, ch);
+      else oct_child_entries<false>(bmin, ext, o, inv, tNear, tFar, ts, ch);
       sort8(ts, ch);
       uint32_t w = 0;
 #pragma unroll
@@ -431,6 +452,7 @@ template <bool COUNT>
 __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
   const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  const bool finiteInv = isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z);
   uint32_t stackRef[BVH_STACK];
   float stackT[BVH_STACK];
   int sp = 0;
@@ -450,10 +472,18 @@ __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float
       const uint32_t child[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
       float t[8];
       uint32_t ch[8];  // sort8 payload = the child word itself (the reference sorts child indices)
+      if (finiteInv) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          t[i] = slab_lane<true>(b[i], b[8 + i], b[16 + i], b[24 + i], b[32 + i], b[40 + i], o, inv, tNear, tFar);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          t[i] = slab_lane<false>(b[i], b[8 + i], b[16 + i], b[24 + i], b[32 + i], b[40 + i], o, inv, tNear, tFar);
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float ti = slab_lane(b[i], b[8 + i], b[16 + i], b[24 + i], b[32 + i], b[40 + i], o, inv, tNear, tFar);
-        t[i] = (child[i] == BVH_EMPTY) ? -1.0f : ti;  // unused lanes behave as misses
+        if (child[i] == BVH_EMPTY) t[i] = -1.0f;  // unused lanes behave as misses
         ch[i] = child[i];
       }
       sort8(t, ch);

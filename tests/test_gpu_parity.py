@@ -202,3 +202,39 @@ def test_edge_cases():
     m = rt.TriangleMesh(v, np.array([0, 1, 2, 3, 4, 5], np.uint32))
     hit, t, n, prim = m.intersect(np.array([[0, 0, 2.5]], np.float32), np.array([[0, 0, -1]], np.float32))
     assert hit[0] and prim[0] == 1 and t[0] == np.float32(2.5)
+
+
+@pytest.mark.parametrize("name", ("sdf_6", "sdf_5", "example_grid", "cube"))
+def test_random_rays_vs_c_oracle(name):
+    """IScene::intersect on 40k seeded rays per scene: from outside, from INSIDE the model's box (every box entry
+    clamps to tNear: sort8 ties), axis-parallel and through exact cell/octant corners."""
+    rng = np.random.default_rng(7)
+    n = 40000
+    o = rng.uniform(-1.6, 1.6, (n, 3)).astype(np.float32)
+    tgt = rng.uniform(-0.7, 0.7, (n, 3)).astype(np.float32)
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    # rays through exact dyadic points along exact diagonals / axes: ties between sibling boxes
+    k = 4000
+    o[:k] = np.float32(2.0) * np.sign(rng.uniform(-1, 1, (k, 3))).astype(np.float32)
+    corner = (rng.integers(-8, 9, (k, 3)) / 8.0).astype(np.float32)
+    dd = corner - o[:k]
+    d[:k] = (dd / np.linalg.norm(dd, axis=1, keepdims=True)).astype(np.float32)
+    o[k:2 * k, 1:] = (rng.integers(-8, 9, (k, 2)) / 8.0).astype(np.float32)
+    o[k:2 * k, 0] = 2.5
+    d[k:2 * k] = np.array([-1.0, 0.0, 0.0], np.float32)
+    ps = util.port_scene(G, name)
+    hit, t, nrm, prim = scene(name).intersect(o, d)
+    bad = 0
+    for i in range(n):
+        h, tt, nn, pp = ps.intersect(o[i], d[i])
+        assert h == bool(hit[i]), f"ray {i}: hit mask"
+        if h:
+            assert util.same_bits(tt, t[i]), f"ray {i}: t {tt} vs {t[i]}"
+            if name != "cube":
+                assert pp == int(prim[i]), f"ray {i}: prim"
+                assert util.same_bits(nn, nrm[i]) or (np.isnan(nn).any() and np.isnan(nrm[i]).any()), f"ray {i}: normal"
+            elif pp != int(prim[i]):
+                bad += 1  # exact ties between the two triangles of a face
+    assert bad <= 0.02 * n

@@ -362,6 +362,50 @@ __device__ __forceinline__ void oct_child_entries(V3 bmin, float ext, V3 o, V3 i
   }
 }
 
+// The same visit list without testing 8 boxes and sorting them.  With no NaN possible, tNear > 0 and no exact
+// ties, the validity test and the sort of ray_pack.ispc:264-271 + raytracing.hpp:188-213 are a pure, exact
+// function of the 9 plane distances (max/min select, they never round), and that function has a closed form:
+// per axis the ray is in the near half on [A, M] and in the far half on [M, B] (A = min, B = max of the outer
+// plane distances, M the centre plane's); inside the node's window [T_in, T_out] = [max(tNear, A's), min(tFar, B's)]
+// the ray starts in the child whose bits are (M_a < T_in) and moves to a neighbour at every M_a inside the window,
+// in increasing M_a.  Those <= 4 children are exactly the boxes whose slab test succeeds, their entry distances are
+// strictly increasing (T_in-side first, then the M_a of each crossing), so sort8 would list them in this order.
+// Any exact tie (two equal centre distances, or one equal to a window end) makes the closed form ambiguous: the
+// caller then falls back to the literal 8-box test + sort8.  Returns false when the fallback is needed.
+__device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 inv, uint32_t nearMask, float tNear,
+                                                  float tFar, uint32_t &w) {
+  const float h = ext * 0.5f;
+  const float ax0 = (bmin.x - o.x) * inv.x, ax1 = (bmin.x + h - o.x) * inv.x, ax2 = (bmin.x + ext - o.x) * inv.x;
+  const float ay0 = (bmin.y - o.y) * inv.y, ay1 = (bmin.y + h - o.y) * inv.y, ay2 = (bmin.y + ext - o.y) * inv.y;
+  const float az0 = (bmin.z - o.z) * inv.z, az1 = (bmin.z + h - o.z) * inv.z, az2 = (bmin.z + ext - o.z) * inv.z;
+  const float tIn = fmaxf(fmaxf(fminf(ax0, ax2), fminf(ay0, ay2)), fmaxf(fminf(az0, az2), tNear));
+  const float tOut = fminf(fminf(fmaxf(ax0, ax2), fmaxf(ay0, ay2)), fminf(fmaxf(az0, az2), tFar));
+  const bool tie = ax1 == ay1 || ax1 == az1 || ay1 == az1 || ax1 == tIn || ay1 == tIn || az1 == tIn || ax1 == tOut ||
+                   ay1 == tOut || az1 == tOut;
+  if (tie) return false;
+  w = 0;
+  if (tIn > tOut) return true;  // the ray misses this node's box inside [tNear, tFar]: no child can be hit
+  // child at the window start, in ray order (bit set = far half), x -> 4, y -> 2, z -> 1 as in divide_box_8
+  uint32_t k = (ax1 < tIn ? 4u : 0u) | (ay1 < tIn ? 2u : 0u) | (az1 < tIn ? 1u : 0u);
+  const float INF = __int_as_float(0x7f800000);
+  float k0 = (tIn < ax1 && ax1 < tOut) ? ax1 : INF, k1 = (tIn < ay1 && ay1 < tOut) ? ay1 : INF,
+        k2 = (tIn < az1 && az1 < tOut) ? az1 : INF;
+  uint32_t m0 = 4u, m1 = 2u, m2 = 1u;
+#define RT_CS3(ka, kb, ma, mb)            \
+  if (ka > kb) {                          \
+    float tf = ka; ka = kb; kb = tf;      \
+    uint32_t tm = ma; ma = mb; mb = tm;   \
+  }
+  RT_CS3(k0, k1, m0, m1) RT_CS3(k1, k2, m1, m2) RT_CS3(k0, k1, m0, m1)
+#undef RT_CS3
+  k ^= nearMask;  // ray order -> spatial child id
+  w = 8u | k;
+  if (k0 < INF) { k ^= m0; w |= (8u | k) << 4; }
+  if (k1 < INF) { k ^= m1; w |= (8u | k) << 8; }
+  if (k2 < INF) { k ^= m2; w |= (8u | k) << 12; }
+  return true;
+}
+
 // SDFOctree::intersectNode, octree_raytracing.cpp:166-202, as an explicit-stack ordered descent.
 // The reference recursion returns as soon as ANY leaf reports a hit (the first hitting child ends every
 // enclosing loop, :188-197), so `hit.t > t` is never evaluated with a hit in hand: the visit rule is just
@@ -373,6 +417,10 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   Hit r = hit_none();
   const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   const bool finiteInv = isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z);
+  // closed-form child list needs: no NaN/inf plane distances, a sign on every axis, and tNear > 0 (so that every
+  // box that passes the slab test also passes the reference's `t > 0` visit rule)
+  const bool fastOk = finiteInv && inv.x != 0.0f && inv.y != 0.0f && inv.z != 0.0f && tNear > 0.0f && tFar >= tNear;
+  const uint32_t nearMask = (inv.x < 0.0f ? 4u : 0u) | (inv.y < 0.0f ? 2u : 0u) | (inv.z < 0.0f ? 1u : 0u);
   uint32_t pend[OCT_MAX_DEPTH + 1];   // pending children of the node at each level
   uint32_t base[OCT_MAX_DEPTH + 1];   // its childrenOffset
   int level = 0;                      // level of `node`
@@ -394,15 +442,19 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
       }
     } else {
       if (COUNT) cnt.oct_inner++;
-      float ts[8];
-      uint32_t ch[8];
-      if (finiteInv) oct_child_entries<true>(bmin, ext, o, inv, tNear, tFar, ts, ch);
-      else oct_child_entries<false>(bmin, ext, o, inv, tNear, tFar, ts, ch);
-      sort8(ts, ch);
       uint32_t w = 0;
+      if (!(fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w))) {
+        // literal path: axis-parallel rays, tNear <= 0, exact ties
+        float ts[8];
+        uint32_t ch[8];
+        if (finiteInv) oct_child_entries<true>(bmin, ext, o, inv, tNear, tFar, ts, ch);
+        else oct_child_entries<false>(bmin, ext, o, inv, tNear, tFar, ts, ch);
+        sort8(ts, ch);
+        w = 0;
 #pragma unroll
-      for (int i = 7; i >= 0; --i)
-        if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
+        for (int i = 7; i >= 0; --i)
+          if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
+      }
       if (w) {
         pend[level] = w;
         base[level] = link;

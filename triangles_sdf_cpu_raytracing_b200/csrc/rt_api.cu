@@ -223,7 +223,7 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
     uint32_t off = link[node];
     if (off == 0) continue;
     if ((uint64_t)off + 7 >= n_nodes) return fail(RT_ERR_INVALID, "octree childrenOffset out of range");
-    if (lvl + 1 > (uint32_t)OCT_MAX_DEPTH) return fail(RT_ERR_INVALID, "octree deeper than the supported 22 levels");
+    if (lvl + 1 > (uint32_t)OCT_MAX_DEPTH) return fail(RT_ERR_INVALID, "octree deeper than the supported 21 levels");
     for (uint32_t c = 0; c < 8; ++c) {
       if (seen[off + c]) return fail(RT_ERR_INVALID, "octree node referenced twice (not a tree)");
       seen[off + c] = 1;

@@ -380,16 +380,18 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
   const float az0 = (bmin.z - o.z) * inv.z, az1 = (bmin.z + h - o.z) * inv.z, az2 = (bmin.z + ext - o.z) * inv.z;
   const float tIn = fmaxf(fmaxf(fminf(ax0, ax2), fminf(ay0, ay2)), fmaxf(fminf(az0, az2), tNear));
   const float tOut = fminf(fminf(fmaxf(ax0, ax2), fmaxf(ay0, ay2)), fminf(fmaxf(az0, az2), tFar));
-  const bool tie = ax1 == ay1 || ax1 == az1 || ay1 == az1 || ax1 == tIn || ay1 == tIn || az1 == tIn || ax1 == tOut ||
-                   ay1 == tOut || az1 == tOut;
+  // crossings strictly inside the window; equal centre distances only matter when both are inside it (two
+  // crossings before T_in just mean "far half on both axes", e.g. a camera on a coordinate axis at the root)
+  const bool ex = tIn < ax1 && ax1 < tOut, ey = tIn < ay1 && ay1 < tOut, ez = tIn < az1 && az1 < tOut;
+  const bool tie = (ex && ey && ax1 == ay1) || (ex && ez && ax1 == az1) || (ey && ez && ay1 == az1) || ax1 == tIn ||
+                   ay1 == tIn || az1 == tIn || ax1 == tOut || ay1 == tOut || az1 == tOut;
   if (tie) return false;
   w = 0;
   if (tIn > tOut) return true;  // the ray misses this node's box inside [tNear, tFar]: no child can be hit
   // child at the window start, in ray order (bit set = far half), x -> 4, y -> 2, z -> 1 as in divide_box_8
   uint32_t k = (ax1 < tIn ? 4u : 0u) | (ay1 < tIn ? 2u : 0u) | (az1 < tIn ? 1u : 0u);
   const float INF = __int_as_float(0x7f800000);
-  float k0 = (tIn < ax1 && ax1 < tOut) ? ax1 : INF, k1 = (tIn < ay1 && ay1 < tOut) ? ay1 : INF,
-        k2 = (tIn < az1 && az1 < tOut) ? az1 : INF;
+  float k0 = ex ? ax1 : INF, k1 = ey ? ay1 : INF, k2 = ez ? az1 : INF;
   uint32_t m0 = 4u, m1 = 2u, m2 = 1u;
 #define RT_CS3(ka, kb, ma, mb)            \
   if (ka > kb) {                          \
@@ -412,6 +414,25 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
 // t > 0 in sort8 order.  Per level we keep one word: the not-yet-visited children in visit order, 4 bits each
 // (bit 3 = valid), and the node's childrenOffset.  Child boxes come from integer (level, i, j, k): the dyadic
 // subdivision of [-1,1] that divide_box_8 (ray_pack.ispc:220-239) computes is exact.
+// ordered list of the children of the inner node with box (bmin, ext) that the ray visits: up to 8 nibbles,
+// first to visit in the low nibble, bit 3 = valid, bits 0..2 = child id
+__device__ __forceinline__ uint32_t oct_children(V3 bmin, float ext, V3 o, V3 inv, bool finiteInv, bool fastOk,
+                                                 uint32_t nearMask, float tNear, float tFar) {
+  uint32_t w = 0;
+  if (fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w)) return w;
+  // literal path: axis-parallel rays, tNear <= 0, exact ties
+  float ts[8];
+  uint32_t ch[8];
+  if (finiteInv) oct_child_entries<true>(bmin, ext, o, inv, tNear, tFar, ts, ch);
+  else oct_child_entries<false>(bmin, ext, o, inv, tNear, tFar, ts, ch);
+  sort8(ts, ch);
+  w = 0;
+#pragma unroll
+  for (int i = 7; i >= 0; --i)
+    if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
+  return w;
+}
+
 template <bool COUNT>
 __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
@@ -421,67 +442,64 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   // box that passes the slab test also passes the reference's `t > 0` visit rule)
   const bool fastOk = finiteInv && inv.x != 0.0f && inv.y != 0.0f && inv.z != 0.0f && tNear > 0.0f && tFar >= tNear;
   const uint32_t nearMask = (inv.x < 0.0f ? 4u : 0u) | (inv.y < 0.0f ? 2u : 0u) | (inv.z < 0.0f ? 1u : 0u);
-  uint32_t pend[OCT_MAX_DEPTH + 1];   // pending children of the node at each level
-  uint32_t base[OCT_MAX_DEPTH + 1];   // its childrenOffset
-  int level = 0;                      // level of `node`
-  uint32_t node = 0, ix = 0, iy = 0, iz = 0;
-  float ext = 2.0f;                   // edge of the current node's box
   V3 hitMin = mk3(0.0f, 0.0f, 0.0f), pHit = hitMin;
   float hitExt = 0.0f;
-  for (;;) {
-    // ---- visit `node` at (level, ix, iy, iz)
-    const uint32_t link = __ldg(oc.link + node);
-    const V3 bmin = mk3(-1.0f + (float)ix * ext, -1.0f + (float)iy * ext, -1.0f + (float)iz * ext);
-    bool descend = false;
-    if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
-      if (COUNT) cnt.oct_leaf++;
-      if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, node, bmin, ext, o, d, inv, tNear, tFar, r, pHit, cnt)) {
-        hitMin = bmin;
-        hitExt = ext;
-        break;
-      }
-    } else {
-      if (COUNT) cnt.oct_inner++;
-      uint32_t w = 0;
-      if (!(fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w))) {
-        // literal path: axis-parallel rays, tNear <= 0, exact ties
-        float ts[8];
-        uint32_t ch[8];
-        if (finiteInv) oct_child_entries<true>(bmin, ext, o, inv, tNear, tFar, ts, ch);
-        else oct_child_entries<false>(bmin, ext, o, inv, tNear, tFar, ts, ch);
-        sort8(ts, ch);
-        w = 0;
-#pragma unroll
-        for (int i = 7; i >= 0; --i)
-          if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
-      }
-      if (w) {
-        pend[level] = w;
-        base[level] = link;
-        descend = true;
-      }
-    }
-    if (!descend) {
-      // ---- climb to the deepest ancestor that still has pending children
-      bool done = false;
-      for (;;) {
-        if (level == 0) { done = true; break; }
+  const uint32_t rootLink = __ldg(oc.link);
+  if (rootLink == OCT_LEAF_SURFACE || rootLink == OCT_LEAF_CULLED) {
+    if (COUNT) cnt.oct_leaf++;
+    hitMin = mk3(-1.0f, -1.0f, -1.0f);
+    hitExt = 2.0f;
+    if (rootLink == OCT_LEAF_SURFACE) oct_leaf<COUNT>(oc, 0, hitMin, 2.0f, o, d, inv, tNear, tFar, r, pHit, cnt);
+  } else {
+    // Iterate the children of the CURRENT inner node from registers; only stepping into an inner child saves
+    // the parent's state (leaf children, the majority of visits, never touch the stack).
+    uint32_t pend[OCT_MAX_DEPTH + 1];  // per level: the parent's not-yet-visited children ...
+    uint32_t base[OCT_MAX_DEPTH + 1];  // ... and its childrenOffset
+    int level = 0;                     // depth of the current inner node
+    V3 bmin = mk3(-1.0f, -1.0f, -1.0f);  // its box: dyadic, so parent/child corners are exact sums
+    float ext = 2.0f;
+    unsigned long long path = 0;       // 3 bits per level: child ids on the way down (for stepping back up)
+    uint32_t cbase = rootLink;
+    if (COUNT) cnt.oct_inner++;
+    uint32_t w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar);
+    for (;;) {
+      if (w == 0) {
+        // ---- back to the parent
+        if (level == 0) break;
         --level;
-        ix >>= 1; iy >>= 1; iz >>= 1;
+        w = pend[level];
+        cbase = base[level];
+        const uint32_t id = (uint32_t)path & 7u;
+        path >>= 3;
+        bmin = mk3(bmin.x - ((id & 4u) ? ext : 0.0f), bmin.y - ((id & 2u) ? ext : 0.0f), bmin.z - ((id & 1u) ? ext : 0.0f));
         ext *= 2.0f;
-        if (pend[level]) break;
+        continue;
       }
-      if (done) break;
+      const uint32_t id = w & 7u;
+      w >>= 4;
+      const uint32_t child = cbase + id;
+      const uint32_t link = __ldg(oc.link + child);
+      const float h = ext * 0.5f;
+      const V3 cmin = mk3(bmin.x + ((id & 4u) ? h : 0.0f), bmin.y + ((id & 2u) ? h : 0.0f), bmin.z + ((id & 1u) ? h : 0.0f));
+      if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
+        if (COUNT) cnt.oct_leaf++;
+        if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, child, cmin, h, o, d, inv, tNear, tFar, r, pHit, cnt)) {
+          hitMin = cmin;
+          hitExt = h;
+          break;  // the first leaf that reports a hit ends the whole descent (octree_raytracing.cpp:188-197)
+        }
+      } else {
+        if (COUNT) cnt.oct_inner++;
+        pend[level] = w;
+        base[level] = cbase;
+        ++level;
+        path = (path << 3) | id;
+        bmin = cmin;
+        ext = h;
+        cbase = link;
+        w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar);
+      }
     }
-    const uint32_t w = pend[level];
-    const uint32_t id = w & 7u;
-    pend[level] = w >> 4;
-    node = base[level] + id;
-    ix = (ix << 1) | (id >> 2);
-    iy = (iy << 1) | ((id >> 1) & 1u);
-    iz = (iz << 1) | (id & 1u);
-    ext *= 0.5f;
-    ++level;
   }
   if (r.hitten) {
     // the hit leaf's normal, evaluated by all lanes that hit together (values are an L1 hit)

@@ -29,7 +29,7 @@ struct GridDev {
 //   otherwise               : childrenOffset of an inner node
 constexpr uint32_t OCT_LEAF_SURFACE = 0u;
 constexpr uint32_t OCT_LEAF_CULLED = 0xFFFFFFFFu;
-constexpr int OCT_MAX_DEPTH = 22;  // child boxes stay exactly representable
+constexpr int OCT_MAX_DEPTH = 21;  // child boxes stay exactly representable; 3 path bits per level in 64
 struct OctreeDev {
   const uint32_t *link;
   const float4 *values;

@@ -84,6 +84,10 @@ typedef struct rt_frame {
   int32_t has_plane;        /* SceneUnion(model, Plane({0,1,0}, plane_y)), main.cpp:189-190 */
   float plane_y;
   float t_near, t_far;      /* raytracing.cpp:90 passes 0.01, 100; 0,0 selects those defaults */
+  /* 1: FrameBuffer::clear() (raytracing.hpp:16-19) is fused into the render: the previous depth is taken as +inf
+   * and pixels the scene does not cover are written with the clear values (colour 0, t = +inf, prim MISS), so one
+   * launch writes every pixel of the call's rows exactly once.  0: the in/out behaviour of Renderer::draw. */
+  int32_t clear;
 } rt_frame;
 
 /* per-frame workload counters (filled when requested; sums over all rays of the call) */

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     # rt_frame: 3+16+16 floats, 5 u32, i32, 3 floats, 3 i32, 1 float, 2 floats
-    assert C.sizeof(rt.RtFrame) == 4 * (3 + 16 + 16 + 5 + 1 + 3 + 3 + 1 + 2)
+    assert C.sizeof(rt.RtFrame) == 4 * (3 + 16 + 16 + 5 + 1 + 3 + 3 + 1 + 2 + 1)
     assert C.sizeof(rt.RtCounters) == 9 * 8
 
 

@@ -238,3 +238,14 @@ def test_random_rays_vs_c_oracle(name):
             elif pp != int(prim[i]):
                 bad += 1  # exact ties between the two triangles of a face
     assert bad <= 0.02 * n
+
+
+def test_fused_clear_equals_clear_then_draw():
+    """rt_frame.clear: FrameBuffer::clear() fused into the render launch; dirty buffers in, the reference's frame out."""
+    for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "cube|default|128x128"):
+        c = G.case(key)
+        dirty_c = np.full((c["H"], c["W"]), 0xDEADBEEF, np.uint32)
+        dirty_t = np.full((c["H"], c["W"]), 0.5, np.float32)
+        r = scene(c["scene"]).render(_frame(c, clear=True), color=dirty_c, t=dirty_t, want_prim=True)
+        assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
+        assert (r["prim"][~np.isfinite(c["t"])] == rt.PRIM_MISS).all()

@@ -26,7 +26,7 @@ class RtFrame(C.Structure):
         ("shading_mode", C.c_int32), ("light_pos", C.c_float * 3),
         ("enable_shadows", C.c_int32), ("enable_reflections", C.c_int32),
         ("has_plane", C.c_int32), ("plane_y", C.c_float),
-        ("t_near", C.c_float), ("t_far", C.c_float),
+        ("t_near", C.c_float), ("t_far", C.c_float), ("clear", C.c_int32),
     ]
 
 

@@ -18,7 +18,7 @@ def _ptr(a):
 
 
 def make_frame(ray_pos, view_inv, proj_inv, W, H, mode=L.SHADE_NORMAL, light=(2.0, 2.0, 2.0), shadows=False,
-               reflections=False, plane_y=None, bands=None, t_near=0.0, t_far=0.0) -> L.RtFrame:
+               reflections=False, plane_y=None, bands=None, t_near=0.0, t_far=0.0, clear=False) -> L.RtFrame:
     """bands = (band_rows, band_count, band_index) selects an interleaved screen-space partition."""
     f = L.RtFrame()
     f.ray_pos[:] = [float(x) for x in np.asarray(ray_pos, np.float32).reshape(3)]
@@ -34,6 +34,7 @@ def make_frame(ray_pos, view_inv, proj_inv, W, H, mode=L.SHADE_NORMAL, light=(2.
     f.has_plane = int(plane_y is not None)
     f.plane_y = float(plane_y) if plane_y is not None else 0.0
     f.t_near, f.t_far = float(t_near), float(t_far)
+    f.clear = int(bool(clear))
     return f
 
 

@@ -360,6 +360,7 @@ int make_frame(const rt_frame *f, FrameDev &d) {
   const bool defaults = f->t_near == 0.0f && f->t_far == 0.0f;
   d.t_near = defaults ? 0.01f : f->t_near;  // raytracing.cpp:90
   d.t_far = defaults ? 100.0f : f->t_far;
+  d.clear = f->clear != 0;
   return RT_OK;
 }
 
@@ -442,8 +443,11 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   cudaStream_t st = s->h_stream;
   RT_CUDA(cudaEventRecord(s->ev[0], st));
   // the framebuffer is in/out (raytracing.cpp:17,90-94): pixels that are not overwritten keep the caller's values
-  RT_CUDA(cudaMemcpyAsync(s->h_t, t_inout, bytes, cudaMemcpyHostToDevice, st));
-  RT_CUDA(cudaMemcpyAsync(s->h_color, color, bytes, cudaMemcpyHostToDevice, st));
+  const bool whole = fd.band_count <= 1;
+  if (!(fd.clear && whole)) {  // a fused clear of the whole frame overwrites every pixel: nothing to upload
+    RT_CUDA(cudaMemcpyAsync(s->h_t, t_inout, bytes, cudaMemcpyHostToDevice, st));
+    RT_CUDA(cudaMemcpyAsync(s->h_color, color, bytes, cudaMemcpyHostToDevice, st));
+  }
   if (prim) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));
   if (counters) RT_CUDA(cudaMemsetAsync(s->h_cnt, 0, sizeof(rt_counters), st));
   RT_CUDA(cudaEventRecord(s->ev[1], st));

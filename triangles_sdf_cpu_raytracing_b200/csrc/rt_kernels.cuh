@@ -187,7 +187,7 @@ __device__ __forceinline__ void shade_pixel(const RenderArgs &a, const float4 *s
   const int y = (int)(f.H - 1u - row);  // loop coordinate of raytracing.cpp:80-82
   const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
   const V3 d = eye_ray(f, (int)x, y);
-  const float tPrev = a.t_in ? a.t_in[px] : __int_as_float(0x7f800000);
+  const float tPrev = (a.t_in && !f.clear) ? a.t_in[px] : __int_as_float(0x7f800000);
   C4 col;
   float tNew;
   uint32_t prim;
@@ -196,6 +196,10 @@ __device__ __forceinline__ void shade_pixel(const RenderArgs &a, const float4 *s
     a.t_out[px] = tNew;
     a.color[px] = color_pack_rgba(col);
     if (a.prim) a.prim[px] = prim;
+  } else if (f.clear) {  // fused FrameBuffer::clear (raytracing.hpp:16-19)
+    a.t_out[px] = __int_as_float(0x7f800000);
+    a.color[px] = 0u;
+    if (a.prim) a.prim[px] = RT_PRIM_MISS;
   }
 }
 

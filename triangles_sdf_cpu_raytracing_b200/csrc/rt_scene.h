@@ -86,6 +86,7 @@ struct FrameDev {
   int32_t shadows, reflections, has_plane;
   float plane_y;
   float t_near, t_far;
+  int32_t clear;
 };
 
 struct RenderArgs {

@@ -231,6 +231,13 @@ def run_cuda(args):
     px = W * H
     color = torch.zeros(px, dtype=torch.int32, device=dev)
     tbuf = torch.full((px,), float("inf"), dtype=torch.float32, device=dev)
+    color_ptr, t_ptr = color.data_ptr(), tbuf.data_ptr()
+    shared = None
+    if world > 1 and args.gather == "p2p":
+        # the root's framebuffer mapped into every rank (CUDA IPC): kernels store their tiles into it over NVLink
+        from triangles_sdf_cpu_raytracing_b200.multigpu import SharedFramebuffer
+        shared = SharedFramebuffer(W, H, root=0)
+        color_ptr, t_ptr = shared.color.value, shared.t.value
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
     n_bands = (H + band_rows - 1) // band_rows
@@ -238,7 +245,7 @@ def run_cuda(args):
 
     def gather_tiles():
         """N > 1: every rank ships its interleaved row bands to rank 0 (NCCL send/recv over NVLink)."""
-        if world == 1:
+        if world == 1 or shared is not None:
             return
         cv = color.view(H, W)
         tv = tbuf.view(H, W)
@@ -269,7 +276,7 @@ def run_cuda(args):
 
     def step():
         # FrameBuffer::clear + Renderer::draw = ONE launch of our kernel
-        scene.render_device(frame, color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
+        scene.render_device(frame, color_ptr, None, t_ptr, stream=stream.cuda_stream)
         gather_tiles()
 
     def barrier():
@@ -320,6 +327,18 @@ def run_cuda(args):
     barrier()
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
 
+    multi_frame = None
+    if world > 1:
+        # the gathered frame of the last step, checked on rank 0 against the oracle below
+        barrier()
+        if rank == 0:
+            if shared is not None:
+                multi_frame = shared.download()
+            else:
+                multi_frame = (color.cpu().numpy().view(np.uint32).reshape(H, W), tbuf.cpu().numpy().reshape(H, W))
+        barrier()
+        if shared is not None:
+            shared.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -386,10 +405,20 @@ def run_cuda(args):
         "vs_baseline": None, "dtype": "f32", "data": "reference scene file (fixture copy), viewer start camera",
         "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal",
                    "math": args.math, "sched": args.sched, "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
-                   "partition": "whole frame" if world == 1 else f"{band_rows}-row bands interleaved over {world} GPUs, NCCL gather to rank 0"},
+                   "partition": "whole frame" if world == 1 else
+                   f"{band_rows}-row bands interleaved over {world} GPUs, " +
+                   ("tiles stored by the render kernel into rank 0's framebuffer over NVLink (CUDA IPC peer mapping)"
+                    if shared is not None else "NCCL send/recv gather to rank 0")},
         "clocks": clk, "gpu_launches": args.steps, "roofline": roofline,
         "counters_per_ray": {k: v / px for k, v in cnt.items()},
     }
+    if multi_frame is not None:
+        want = oracle_frame(g, scene_name, c, W, H)
+        if want is not None:
+            d = util.compare_frames(multi_frame[0], multi_frame[1], want[0], want[1])
+            d["bit_identical"] = bool(util.same_bits(multi_frame[1], want[1]) and np.array_equal(multi_frame[0], want[0]))
+            d["checker"] = want[2]
+            line["parity"] = d
     if e2e is not None:
         line["e2e"] = e2e
         line["cpu_baseline"] = cpu_baseline(g, scene_name, c, W, H)
@@ -415,6 +444,8 @@ def main():
     ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=("exact", "fast"))
     ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    ap.add_argument("--gather", default="p2p", choices=("p2p", "nccl"),
+                    help="N > 1: how tiles reach rank 0 (fused peer stores, or an NCCL send/recv gather)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

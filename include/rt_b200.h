@@ -156,6 +156,23 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
                       float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
                       uint32_t *prim);
 
+/* ---- device buffers and cross-process sharing (multi-GPU: one process per GPU) ----------------------- */
+/* The reference has one framebuffer in one address space.  With one process per GPU the root rank owns the
+ * framebuffer (rt_device_malloc on its GPU), exports it (CUDA IPC), and every other rank opens it and passes the
+ * mapped pointers to rt_render_device: its tiles are then stored straight into the root framebuffer over
+ * NVLink / NVSwitch by the render kernel itself (no separate gather collective).
+ * handle = 64 opaque bytes (cudaIpcMemHandle_t). */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_device_malloc(uint64_t bytes, void **dev_ptr);            /* on the calling thread's current device */
+int rt_device_free(void *dev_ptr);
+int rt_ipc_export(const void *dev_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]);
+int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dev_ptr); /* enables peer access lazily */
+int rt_ipc_close(void *dev_ptr);
+/* stream-ordered copies between host and device buffers (stream = cudaStream_t as void*, NULL = default stream;
+ * the call returns after the copy has completed) */
+int rt_memcpy_d2h(void *host, const void *dev_ptr, uint64_t bytes, void *stream);
+int rt_memcpy_h2d(void *dev_ptr, const void *host, uint64_t bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

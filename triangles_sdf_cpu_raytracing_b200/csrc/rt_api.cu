@@ -511,3 +511,63 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
 }
 
 }  // extern "C"
+
+// =============================================================================================================
+// device buffers + CUDA IPC (one process per GPU; tiles are stored into the root's framebuffer over NVLink)
+// =============================================================================================================
+extern "C" {
+
+int rt_device_malloc(uint64_t bytes, void **dev_ptr) {
+  if (!dev_ptr) return fail(RT_ERR_INVALID, "dev_ptr is null");
+  *dev_ptr = nullptr;
+  RT_CUDA(cudaMalloc(dev_ptr, bytes ? bytes : 1));
+  return RT_OK;
+}
+
+int rt_device_free(void *dev_ptr) {
+  RT_CUDA(cudaFree(dev_ptr));
+  return RT_OK;
+}
+
+int rt_ipc_export(const void *dev_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "IPC handle size");
+  if (!dev_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
+  cudaIpcMemHandle_t h;
+  RT_CUDA(cudaIpcGetMemHandle(&h, const_cast<void *>(dev_ptr)));
+  std::memcpy(handle, &h, sizeof h);
+  return RT_OK;
+}
+
+int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dev_ptr) {
+  if (!dev_ptr || !handle) return fail(RT_ERR_INVALID, "null argument");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof h);
+  *dev_ptr = nullptr;
+  RT_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RT_OK;
+}
+
+int rt_ipc_close(void *dev_ptr) {
+  RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  return RT_OK;
+}
+
+int rt_memcpy_d2h(void *host, const void *dev_ptr, uint64_t bytes, void *stream) {
+  if (bytes == 0) return RT_OK;
+  if (!host || !dev_ptr) return fail(RT_ERR_INVALID, "null argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RT_CUDA(cudaMemcpyAsync(host, dev_ptr, bytes, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaStreamSynchronize(st));
+  return RT_OK;
+}
+
+int rt_memcpy_h2d(void *dev_ptr, const void *host, uint64_t bytes, void *stream) {
+  if (bytes == 0) return RT_OK;
+  if (!host || !dev_ptr) return fail(RT_ERR_INVALID, "null argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  RT_CUDA(cudaMemcpyAsync(dev_ptr, host, bytes, cudaMemcpyHostToDevice, st));
+  RT_CUDA(cudaStreamSynchronize(st));
+  return RT_OK;
+}
+
+}  // extern "C"

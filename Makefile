@@ -7,8 +7,22 @@ NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall
 OUT   := $(PKG)/librt_b200.so
 OBJ   := $(CSRC)/build
 
-$(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o
+HOST  := $(PKG)/hostapi
+EXAMPLE := $(HOST)/example_frame_loop
+
+all: $(OUT) $(EXAMPLE)
+
+$(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o $(OBJ)/rt_host.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart shared
+
+# host mirror of the reference's C++ interface (pure host code; -ffp-contract=off keeps the camera matrices
+# bit-identical to the reference's)
+$(OBJ)/rt_host.o: $(HOST)/rt_host.cpp $(HOST)/scenes.hpp $(HOST)/raytracing.hpp $(HOST)/camera.hpp $(HOST)/rt_math.hpp include/rt_b200.h include/rt_b200_host.h
+	@mkdir -p $(OBJ)
+	g++ -std=c++17 -O2 -ffp-contract=off -fPIC -Wall -Wextra -c $< -o $@
+
+$(EXAMPLE): $(HOST)/example_frame_loop.cpp $(HOST)/scenes.hpp $(HOST)/raytracing.hpp $(HOST)/camera.hpp $(HOST)/rt_math.hpp $(OUT)
+	g++ -std=c++17 -O2 -ffp-contract=off -Wall -Wextra -o $@ $< -L$(PKG) -lrt_b200 -Wl,-rpath,'$$ORIGIN/..'
 
 $(OBJ)/rt_kernels_exact.o: $(CSRC)/rt_kernels_exact.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
 	@mkdir -p $(OBJ)
@@ -28,4 +42,4 @@ $(OBJ)/bvh_builder.o: $(CSRC)/bvh_builder.cpp $(CSRC)/bvh_builder.h $(CSRC)/rt_s
 
 .PHONY: clean
 clean:
-	rm -rf $(OBJ) $(OUT)
+	rm -rf $(OBJ) $(OUT) $(EXAMPLE)

@@ -385,9 +385,11 @@ def run_cuda(args):
         chk_t = ht.numpy().reshape(H, W).copy()
 
     # ---- workload counters + roofline of the dominant (only) kernel
-    r = scene.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), want_counters=True)
+    # (N > 1: rank 0's share of the frame, the part its kernel launch actually processes)
+    r = scene.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands), want_counters=True)
     cnt = r["counters"]
-    alg_bytes, alg_flops = algorithmic_work(kind, cnt, px)
+    rays_launch = max(1, cnt["rays"])
+    alg_bytes, alg_flops = algorithmic_work(kind, cnt, rays_launch)
     hbm, peak_kind, sm_max = peaks()
     clk = clocks.summary()
     fp32_peak = 148 * 128 * 2 * (clk["sm_mhz"] or sm_max) * 1e6 / 1e12  # TFLOP/s at the clock seen under load
@@ -396,6 +398,7 @@ def run_cuda(args):
                 "traffic": None, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
                 "kernel_ms": kernel_ms, "kernel_ms_warm_l2": kernel_ms_warm,
                 "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_flops_per_launch": alg_flops,
+                "rays_per_launch": rays_launch,
                 "fp32": {"achieved_tflops": alg_flops / (kernel_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                          "frac": alg_flops / (kernel_ms * 1e-3) / 1e12 / fp32_peak},
                 "note": "scene fits in L2: the operative bounds are cached-gather latency and the FP32 pipe, see DESIGN.md"}
@@ -410,7 +413,7 @@ def run_cuda(args):
                    ("tiles stored by the render kernel into rank 0's framebuffer over NVLink (CUDA IPC peer mapping)"
                     if shared is not None else "NCCL send/recv gather to rank 0")},
         "clocks": clk, "gpu_launches": args.steps, "roofline": roofline,
-        "counters_per_ray": {k: v / px for k, v in cnt.items()},
+        "counters_per_ray": {k: v / rays_launch for k, v in cnt.items()},
     }
     if multi_frame is not None:
         want = oracle_frame(g, scene_name, c, W, H)

@@ -112,6 +112,16 @@ def save_frames(o: R.RefOracle):
             tp, _n, prim = s.render_prim(cams[cam], W, H)
             assert np.array_equal(tp, t)
             out[key + "|prim"] = prim
+        # the viewer's default look: Lambert + shadow rays + reflections + checkerboard ground plane
+        if cam in ("default", "orbit5", "close"):
+            plane_y = s.model_min_y if s.kind == R.KIND_MESH else -1.0  # main.cpp:176-189
+            full = s.with_plane(plane_y)
+            col, tf, _ = full.render(cams[cam], W, H, mode=R.MODE_LAMBERT, shadows=True, reflections=True)
+            out[key + "|color_full"] = col
+            out[key + "|t_full"] = tf
+            out[key + "|plane_y"] = np.float32(plane_y)
+            col, _, _ = s.render(cams[cam], W, H, mode=R.MODE_LAMBERT, shadows=True, reflections=False)
+            out[key + "|color_shadow"] = col
         # in/out depth buffer: a pre-filled depth plane at t=2.2 hides farther hits
         t0 = np.full((H, W), 2.2, np.float32)
         c0 = np.full((H, W), 0x11223344, np.uint32)

@@ -28,7 +28,8 @@ class Golden:
         g = lambda n: self.frames[f"{key}|{n}"] if f"{key}|{n}" in self.frames else None  # noqa: E731
         return dict(scene=scene, cam=cam, W=W, H=H, rayPos=g("rayPos"), viewInv=g("viewInv"), projInv=g("projInv"),
                     color_normal=g("color_normal"), color_lambert=g("color_lambert"), color_color=g("color_color"),
-                    t=g("t"), prim=g("prim"), color_prefilled=g("color_prefilled"), t_prefilled=g("t_prefilled"))
+                    t=g("t"), prim=g("prim"), color_prefilled=g("color_prefilled"), t_prefilled=g("t_prefilled"),
+                    color_full=g("color_full"), t_full=g("t_full"), plane_y=g("plane_y"), color_shadow=g("color_shadow"))
 
 
 def port_scene(golden: Golden, name: str):

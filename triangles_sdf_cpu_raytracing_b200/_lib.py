@@ -67,6 +67,12 @@ SIGNATURES = {
     "rt_ipc_close": (_i, [_vp]),
     "rt_memcpy_d2h": (_i, [_vp, _vp, C.c_uint64, _vp]),
     "rt_memcpy_h2d": (_i, [_vp, _vp, C.c_uint64, _vp]),
+    # include/rt_b200_host.h
+    "rt_host_camera": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp, _vp]),
+    "rt_host_projection": (_i, [_f, _f, _f, _f, _vp, _vp]),
+    "rt_host_load_obj": (_i, [C.c_char_p, _i, C.POINTER(C.POINTER(_f)), C.POINTER(_u32),
+                              C.POINTER(C.POINTER(_u32)), C.POINTER(_u32)]),
+    "rt_host_free": (None, [_vp]),
 }
 
 _lib = None

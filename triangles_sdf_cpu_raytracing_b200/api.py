@@ -173,3 +173,37 @@ def set_math_mode(mode: int):
 
 def set_sched_mode(mode: int):
     L.check(L.lib().rt_set_sched_mode(mode))
+
+
+# ---- host mirror hooks (include/rt_b200_host.h): the reference's Camera / projection / OBJ loading, host only
+def host_camera(eye=(0.0, 0.0, 2.5), target=(0.0, 0.0, 0.0), up=(0.0, 1.0, 0.0), lock_up=True, n_rotate=0, dx=0.0,
+                dy=0.0):
+    """Camera(eye, target, up) + setLockUp + n x rotate(dx, dy) -> (position[3], view[16], viewInv[16])."""
+    a = [np.ascontiguousarray(x, np.float32) for x in (eye, target, up)]
+    pos, view, vinv = np.zeros(3, np.float32), np.zeros(16, np.float32), np.zeros(16, np.float32)
+    L.check(L.lib().rt_host_camera(_ptr(a[0]), _ptr(a[1]), _ptr(a[2]), int(lock_up), int(n_rotate), float(dx),
+                                   float(dy), _ptr(pos), _ptr(view), _ptr(vinv)))
+    return pos, view, vinv
+
+
+def host_projection(W, H, fovy=45.0, z_near=0.01, z_far=100.0):
+    """main.cpp:198-201 -> (proj[16], projInv[16])."""
+    proj, inv = np.zeros(16, np.float32), np.zeros(16, np.float32)
+    aspect = float(np.float32(W) / np.float32(H))
+    L.check(L.lib().rt_host_projection(fovy, aspect, z_near, z_far, _ptr(proj), _ptr(inv)))
+    return proj, inv
+
+
+def host_load_obj(path: str, scale: bool = True):
+    """LoadMeshFromObj (+ loadAndScale) -> (vpos4 [n,4] f32, indices [m] u32)."""
+    pv, pi = C.POINTER(C.c_float)(), C.POINTER(C.c_uint32)()
+    nv, ni = C.c_uint32(), C.c_uint32()
+    if L.lib().rt_host_load_obj(path.encode(), int(scale), C.byref(pv), C.byref(nv), C.byref(pi), C.byref(ni)) != 0:
+        raise L.RtError(f"cannot load {path}")
+    try:
+        v = np.ctypeslib.as_array(pv, shape=(nv.value, 4)).copy()
+        i = np.ctypeslib.as_array(pi, shape=(ni.value,)).copy()
+    finally:
+        L.lib().rt_host_free(pv)
+        L.lib().rt_host_free(pi)
+    return v, i

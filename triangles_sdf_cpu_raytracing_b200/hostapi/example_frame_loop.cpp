@@ -1,0 +1,76 @@
+// The viewer's frame loop (src/main.cpp:89-91, 196-208) without the window: same classes, same calls.
+//   example_frame_loop <scene.grid|.octree|.obj> <W> <H> <normal|lambert|color> <plane 0|1> <out.raw> [orbit steps]
+// out.raw = W*H uint32 colour followed by W*H float depth (the FrameBuffer contents after draw).
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <memory>
+#include <string>
+
+#include "scenes.hpp"
+
+static bool ends_with(const std::string &s, const char *suf) {
+  size_t n = std::strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+int main(int argc, char **argv) {
+  if (argc < 7) {
+    std::fprintf(stderr, "usage: %s scene W H normal|lambert|color plane out.raw [orbit steps]\n", argv[0]);
+    return 2;
+  }
+  try {
+    const std::string path = argv[1];
+    const uint32_t W = std::atoi(argv[2]), H = std::atoi(argv[3]);
+    const std::string mode = argv[4];
+    const bool plane = std::atoi(argv[5]) != 0;
+    const int orbit = argc > 7 ? std::atoi(argv[7]) : 0;
+
+    std::shared_ptr<IScene> pScene;  // main.cpp:167-191
+    float planeY = -1.0f;
+    if (ends_with(path, ".grid")) {
+      auto g = std::make_shared<SDFGrid>();
+      loadSDFGrid(*g, path);
+      pScene = g;
+    } else if (ends_with(path, ".octree")) {
+      auto o = std::make_shared<SDFOctree>();
+      loadSDFOctree(*o, path);
+      pScene = o;
+    } else {
+      auto b = std::make_shared<BVHBuilder>();
+      b->perform(loadAndScale(path));
+      planeY = b->modelMinY();
+      pScene = b;
+    }
+    std::shared_ptr<IScene> fullScene =
+        std::make_shared<SceneUnion>(pScene, std::make_shared<Plane>(rtmath::float3{0.0f, 1.0f, 0.0f}, planeY));
+
+    FrameBuffer frameBuf;
+    frameBuf.resize(W, H);
+    Camera camera({0.0f, 0.0f, 2.5f}, {0.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f});  // main.cpp:89-91
+    camera.setLockUp(true);
+    Renderer renderer;
+    renderer.lightPos = {2.0f, 2.0f, 2.0f};  // main.cpp:60
+    renderer.shadingMode = mode == "normal" ? ShadingMode::Normal : mode == "color" ? ShadingMode::Color : ShadingMode::Lambert;
+    renderer.enableShadows = plane;
+    renderer.enableReflections = plane;
+
+    float time = 0.0f;
+    for (int frame = 0; frame <= orbit; ++frame) {
+      // one 64th of a full orbit per frame: rotate() multiplies by the 0.01 sensitivity (camera.hpp:55)
+      if (frame > 0) camera.rotate(static_cast<float>(2.0 * 3.14159265358979323846 / 64.0 / 0.01), 0.0f);
+      frameBuf.clear();  // main.cpp:197
+      auto proj = rtmath::perspectiveMatrix(45.0f, static_cast<float>(W) / static_cast<float>(H), 0.01f, 100.0f);
+      auto projInv = rtmath::inverse4x4(proj);  // main.cpp:198-201
+      time = renderer.draw(plane ? *fullScene : *pScene, frameBuf, camera, projInv);  // main.cpp:203 / 206
+    }
+    std::ofstream out(argv[6], std::ios::binary);
+    out.write(reinterpret_cast<const char *>(frameBuf.color.data()), static_cast<std::streamsize>(W) * H * 4);
+    out.write(reinterpret_cast<const char *>(frameBuf.t.data()), static_cast<std::streamsize>(W) * H * 4);
+    std::printf("Render Time: %.3f ms\n", time);
+    return 0;
+  } catch (const std::exception &e) {
+    std::fprintf(stderr, "error: %s\n", e.what());
+    return 1;
+  }
+}

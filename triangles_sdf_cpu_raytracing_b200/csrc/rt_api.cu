@@ -69,8 +69,9 @@ struct rt_scene {
   uint32_t *h_prim = nullptr;
   rt_counters *h_cnt = nullptr;
   size_t h_pixels = 0;
-  cudaStream_t h_stream = nullptr;
+  cudaStream_t h_stream = nullptr, h_up = nullptr, h_down = nullptr;  // kernels, H2D copies, D2H copies
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_up[16] = {}, ev_k[16] = {};  // per row chunk: upload done, kernel done
 };
 
 namespace {
@@ -125,7 +126,13 @@ void scene_free(rt_scene *s) {
   if (s->h_cnt) cudaFree(s->h_cnt);
   for (auto &e : s->ev)
     if (e) cudaEventDestroy(e);
+  for (auto &e : s->ev_up)
+    if (e) cudaEventDestroy(e);
+  for (auto &e : s->ev_k)
+    if (e) cudaEventDestroy(e);
   if (s->h_stream) cudaStreamDestroy(s->h_stream);
+  if (s->h_up) cudaStreamDestroy(s->h_up);
+  if (s->h_down) cudaStreamDestroy(s->h_down);
   delete s;
 }
 
@@ -394,7 +401,11 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
 int ensure_host_buffers(rt_scene *s, size_t pixels) {
   if (!s->h_stream) {
     RT_CUDA(cudaStreamCreateWithFlags(&s->h_stream, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&s->h_up, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&s->h_down, cudaStreamNonBlocking));
     for (auto &e : s->ev) RT_CUDA(cudaEventCreate(&e));
+    for (auto &e : s->ev_up) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : s->ev_k) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     RT_CUDA(cudaMalloc(&s->h_cnt, sizeof(rt_counters)));
   }
   if (pixels > s->h_pixels) {
@@ -441,25 +452,51 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   rc = ensure_host_buffers(s, pixels);
   if (rc) return rc;
   cudaStream_t st = s->h_stream;
-  RT_CUDA(cudaEventRecord(s->ev[0], st));
-  // the framebuffer is in/out (raytracing.cpp:17,90-94): pixels that are not overwritten keep the caller's values
+  // The frame is cut into row chunks that flow through three streams: upload (only when the caller's depth /
+  // colour matter: the framebuffer is in/out, raytracing.cpp:17,90-94), render, download.  The PCIe copies of one
+  // chunk overlap the kernel of the next, so the call costs ~max(copy time, kernel time), not their sum.
   const bool whole = fd.band_count <= 1;
-  if (!(fd.clear && whole)) {  // a fused clear of the whole frame overwrites every pixel: nothing to upload
-    RT_CUDA(cudaMemcpyAsync(s->h_t, t_inout, bytes, cudaMemcpyHostToDevice, st));
-    RT_CUDA(cudaMemcpyAsync(s->h_color, color, bytes, cudaMemcpyHostToDevice, st));
-  }
-  if (prim) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));
+  const bool need_upload = !(fd.clear && whole);  // a fused clear of the whole frame overwrites every pixel
+  uint32_t n_chunks = 1;
+  if (whole && fd.H >= 64) n_chunks = std::min<uint32_t>(16u, std::max<uint32_t>(1u, fd.H / 128u));
+  const uint32_t chunk_rows = (fd.H + n_chunks - 1) / n_chunks;
+  RT_CUDA(cudaEventRecord(s->ev[0], st));
+  if (prim && need_upload) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));  // rows not rendered: MISS
   if (counters) RT_CUDA(cudaMemsetAsync(s->h_cnt, 0, sizeof(rt_counters), st));
   RT_CUDA(cudaEventRecord(s->ev[1], st));
-  rc = render_on_stream(s, fd, s->h_color, s->h_t, s->h_t, prim ? s->h_prim : nullptr, counters ? s->h_cnt : nullptr, st);
-  if (rc) return rc;
+  RT_CUDA(cudaStreamWaitEvent(s->h_up, s->ev[0], 0));
+  for (uint32_t k = 0; k < n_chunks; ++k) {
+    const uint32_t r0 = k * chunk_rows, r1 = std::min(fd.H, r0 + chunk_rows);
+    if (r0 >= r1) break;
+    const size_t off = (size_t)r0 * fd.W, cbytes = (size_t)(r1 - r0) * fd.W * 4;
+    FrameDev fk = fd;
+    if (n_chunks > 1) {  // chunk k = band k of a (chunk_rows, n_chunks) partition
+      fk.band_rows = chunk_rows;
+      fk.band_count = n_chunks;
+      fk.band_index = k;
+      fk.rows_here = chunk_rows;
+    }
+    if (need_upload) {
+      const size_t uoff = n_chunks > 1 ? off : 0, ubytes = n_chunks > 1 ? cbytes : bytes;
+      RT_CUDA(cudaMemcpyAsync(s->h_t + uoff, t_inout + uoff, ubytes, cudaMemcpyHostToDevice, s->h_up));
+      RT_CUDA(cudaMemcpyAsync(s->h_color + uoff, color + uoff, ubytes, cudaMemcpyHostToDevice, s->h_up));
+      RT_CUDA(cudaEventRecord(s->ev_up[k], s->h_up));
+      RT_CUDA(cudaStreamWaitEvent(st, s->ev_up[k], 0));
+    }
+    rc = render_on_stream(s, fk, s->h_color, s->h_t, s->h_t, prim ? s->h_prim : nullptr, counters ? s->h_cnt : nullptr, st);
+    if (rc) return rc;
+    RT_CUDA(cudaEventRecord(s->ev_k[k], st));
+    RT_CUDA(cudaStreamWaitEvent(s->h_down, s->ev_k[k], 0));
+    const size_t doff = n_chunks > 1 ? off : 0, dbytes = n_chunks > 1 ? cbytes : bytes;
+    RT_CUDA(cudaMemcpyAsync(color + doff, s->h_color + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
+    RT_CUDA(cudaMemcpyAsync(t_inout + doff, s->h_t + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
+    if (prim) RT_CUDA(cudaMemcpyAsync(prim + doff, s->h_prim + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
+  }
   RT_CUDA(cudaEventRecord(s->ev[2], st));
-  RT_CUDA(cudaMemcpyAsync(color, s->h_color, bytes, cudaMemcpyDeviceToHost, st));
-  RT_CUDA(cudaMemcpyAsync(t_inout, s->h_t, bytes, cudaMemcpyDeviceToHost, st));
-  if (prim) RT_CUDA(cudaMemcpyAsync(prim, s->h_prim, bytes, cudaMemcpyDeviceToHost, st));
   if (counters) RT_CUDA(cudaMemcpyAsync(counters, s->h_cnt, sizeof(rt_counters), cudaMemcpyDeviceToHost, st));
-  RT_CUDA(cudaEventRecord(s->ev[3], st));
   RT_CUDA(cudaStreamSynchronize(st));
+  RT_CUDA(cudaEventRecord(s->ev[3], s->h_down));
+  RT_CUDA(cudaStreamSynchronize(s->h_down));
   if (device_ms) RT_CUDA(cudaEventElapsedTime(device_ms, s->ev[1], s->ev[2]));
   if (total_ms) RT_CUDA(cudaEventElapsedTime(total_ms, s->ev[0], s->ev[3]));
   return RT_OK;

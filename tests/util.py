@@ -18,8 +18,24 @@ class Golden:
         self._scenes = {}
 
     def scene_arrays(self, name):
+        """Fixture copy of a shipped resource, or a deterministic stand-in derived from one (standins.py):
+        example_grid_x4 / _x8 (257^3 / 513^3 refinements), octree_d8 / octree_d9 (octrees of those grids),
+        stanford-bunny_s1 / _s2 (x4 / x16 midpoint subdivisions)."""
         if name not in self._scenes:
-            self._scenes[name] = dict(np.load(os.path.join(GOLDEN, "scenes", f"{name}.npz")))
+            from triangles_sdf_cpu_raytracing_b200 import standins as S
+            if name.startswith("example_grid_x"):
+                a = dict(values=S.refine_grid(self.scene_arrays("example_grid")["values"], int(name.rsplit("x", 1)[1])))
+            elif name.startswith("octree_d"):
+                d = int(name.rsplit("d", 1)[1])
+                grid = S.refine_grid(self.scene_arrays("example_grid")["values"], (1 << d) // 64)
+                a = dict(nodes36=S.octree_from_grid(grid, d))
+            elif name.startswith("stanford-bunny_s"):
+                m = self.scene_arrays("stanford-bunny")
+                v, i = S.subdivide_mesh(m["vpos4"], m["indices"], int(name.rsplit("s", 1)[1]))
+                a = dict(vpos4=v, indices=i)
+            else:
+                a = dict(np.load(os.path.join(GOLDEN, "scenes", f"{name}.npz")))
+            self._scenes[name] = a
         return self._scenes[name]
 
     def case(self, key):

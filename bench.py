@@ -32,7 +32,16 @@ WORKLOADS = {
     "octree6_4k": ("sdf_6", "sdf_6|default|160x90", 3840, 2160),
     "bunny_4k": ("stanford-bunny", "stanford-bunny|default|160x90", 3840, 2160),
     "grid65_4k": ("example_grid", "example_grid|default|160x90", 3840, 2160),
+    # deterministic stand-ins for the resources the reference tree does not ship (standins.py)
+    "grid257_4k": ("example_grid_x4", "example_grid|default|160x90", 3840, 2160),   # configs[2], 68 MB: L2-resident
+    "grid513_4k": ("example_grid_x8", "example_grid|default|160x90", 3840, 2160),   # configs[2], 540 MB: HBM-resident
+    "octree8_4k": ("octree_d8", "example_grid|default|160x90", 3840, 2160),         # configs[3]
+    "octree9_4k": ("octree_d9", "example_grid|default|160x90", 3840, 2160),         # configs[3]
+    "bunny_s2_4k": ("stanford-bunny_s2", "example_grid|default|160x90", 3840, 2160),  # configs[4] mesh, 1.1 M triangles
+    # configs[4]: step k renders frame k % 64 of the orbit (Camera::rotate(2*pi/64/0.01, 0) k times, camera.cpp:5-20)
+    "bunny_s2_orbit64_4k": ("stanford-bunny_s2", "example_grid|default|160x90", 3840, 2160),
 }
+ORBIT_DX = float(np.float32(2.0 * np.pi / 64.0 / 0.01))
 HEADLINE = "grid65_1080p"
 METRIC = "Mrays/s primary rays"
 L2_FLUSH_BYTES = 256 << 20
@@ -107,10 +116,12 @@ def run_reference(args):
         o.set_threads(cores)
         a = g.scene_arrays(scene_name)
         s = o.grid(a["values"]) if "values" in a else o.octree(a["nodes36"]) if "nodes36" in a else o.mesh(a["vpos4"], a["indices"])
-        cam = R.CamSpec()
         kind = "reference"
+        orbit = [0]
 
         def rows(y0, y1):
+            cam = R.CamSpec(n_rotate=orbit[0] % 64, dx=ORBIT_DX, dy=0.0) if "orbit" in args.scene else R.CamSpec()
+            orbit[0] += 1
             return s.render_rows(cam, W, H, y0, y1, proj_inv=c["projInv"])[2]
     else:
         from oracle import port_oracle as P
@@ -149,7 +160,7 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ CUDA arm
-def cpu_baseline(g, scene_name, c, W, H):
+def cpu_baseline(g, scene_name, c, W, H, orbit=False):
     """Rank 0, N=1: the reference's CPU path timed on this box's host cores on a bounded sample."""
     from oracle import ref_oracle as R
     cores = os.cpu_count() or 1
@@ -159,6 +170,13 @@ def cpu_baseline(g, scene_name, c, W, H):
             o.set_threads(cores)
             a = g.scene_arrays(scene_name)
             s = o.grid(a["values"]) if "values" in a else o.octree(a["nodes36"]) if "nodes36" in a else o.mesh(a["vpos4"], a["indices"])
+            if orbit:
+                ks = (0, 16, 32, 48)
+                ms = [s.render_timed(R.CamSpec(n_rotate=k, dx=ORBIT_DX, dy=0.0), W, H, frames=2, proj_inv=c["projInv"])[0]
+                      for k in ks]
+                return {"value": W * H / float(np.mean(ms)) / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "reference",
+                        "sample": f"orbit frames {ks} of 64 at {W}x{H} through the reference's Renderer::draw (best of 2 "
+                                  f"each, mean over the 4 cameras), scalar ISPC stand-in"}
             best, each = s.render_timed(R.CamSpec(), W, H, frames=3, proj_inv=c["projInv"])
             return {"value": W * H / best / 1e3, "unit": "Mrays/s", "cores": cores, "kind": "reference",
                     "sample": f"3 full {W}x{H} frames through the reference's Renderer::draw (best), scalar ISPC stand-in"}
@@ -222,12 +240,23 @@ def run_cuda(args):
     rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT}[args.sched])
 
     g, scene_name, c, W, H = load_workload(args.scene)
-    scene = util.cuda_scene(g, scene_name)
+    t_build = time.perf_counter()
+    layout_kw = {}
+    if args.grid_layout != "auto":
+        layout_kw = {"layout": {"linear": rt.GRID_LINEAR, "bricks": rt.GRID_BRICKS}[args.grid_layout]}
+    scene = util.cuda_scene(g, scene_name, **layout_kw)
+    t_build = time.perf_counter() - t_build
     kind = {0: "grid", 1: "octree", 2: "mesh"}[scene.kind]
     band_rows = 32
     bands = (band_rows, world, rank) if world > 1 else None
     # FrameBuffer::clear (raytracing.hpp:16-19) is fused into the render launch: one kernel writes every pixel once
     frame = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands, clear=True)
+    frames = [frame]
+    orbit = "orbit" in args.scene
+    if orbit:  # the 64 cameras of the orbit, from the host mirror of the reference's Camera (camera.cpp:5-20)
+        cams = [rt.host_camera(n_rotate=k, dx=ORBIT_DX, dy=0.0) for k in range(64)]
+        frames = [rt.make_frame(pos, vinv, c["projInv"], W, H, bands=bands, clear=True) for pos, _v, vinv in cams]
+    step_no = [0]
     px = W * H
     color = torch.zeros(px, dtype=torch.int32, device=dev)
     tbuf = torch.full((px,), float("inf"), dtype=torch.float32, device=dev)
@@ -276,7 +305,8 @@ def run_cuda(args):
 
     def step():
         # FrameBuffer::clear + Renderer::draw = ONE launch of our kernel
-        scene.render_device(frame, color_ptr, None, t_ptr, stream=stream.cuda_stream)
+        scene.render_device(frames[step_no[0] % len(frames)], color_ptr, None, t_ptr, stream=stream.cuda_stream)
+        step_no[0] += 1
         gather_tiles()
 
     def barrier():
@@ -287,6 +317,7 @@ def run_cuda(args):
     for _ in range(max(3, args.warmup)):
         step()
     barrier()
+    step_no[0] = 0
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     with ClockSampler(local) as clocks:
         barrier()
@@ -310,18 +341,18 @@ def run_cuda(args):
     barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for _ in range(args.steps):
-        scene.render_device(frame, color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
+    for i in range(args.steps):
+        scene.render_device(frames[i % len(frames)], color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
     b.record()
     barrier()
     kernel_ms_warm = a.elapsed_time(b) / args.steps
     # kernel alone, cold L2 (the roofline's launch duration)
     kev = []
-    for _ in range(min(args.steps, 50)):
+    for i in range(min(args.steps, 64)):
         flush.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        scene.render_device(frame, color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
+        scene.render_device(frames[i % len(frames)], color.data_ptr(), None, tbuf.data_ptr(), stream=stream.cuda_stream)
         b.record()
         kev.append((a, b))
     barrier()
@@ -354,15 +385,13 @@ def run_cuda(args):
         dms, tms = C.c_float(), C.c_float()
         n_e2e = max(5, min(args.steps, 30))
 
-        def time_host(fr, preclear):
+        def time_host(fr, before):
+            """before(i): what the CPU does to the host framebuffer between two calls (untimed, like the reference's own
+            stopwatch which only brackets draw).  It matters: cache lines the CPU has just written are dirty and the
+            DMA write that follows has to evict them first."""
             times = []
             for i in range(n_e2e + 3):
-                if preclear:  # the caller's FrameBuffer::clear() on the host (untimed: the reference's draw excludes it too)
-                    hc.zero_()
-                    ht.fill_(float("inf"))
-                else:         # dirty buffers: the fused clear must overwrite every pixel
-                    hc.fill_(0x5A5A5A5A)
-                    ht.fill_(0.25)
+                before()
                 t0 = time.perf_counter()
                 L.check(L.lib().rt_render_host(scene.handle, C.byref(fr), C.c_void_p(hc.data_ptr()),
                                                C.c_void_p(ht.data_ptr()), None, C.byref(dms), C.byref(tms), None))
@@ -370,44 +399,86 @@ def run_cuda(args):
                     times.append((time.perf_counter() - t0) * 1e3)
             return float(np.mean(times))
 
-        # (a) the reference's literal in/out contract: depth + colour go up, both come back
-        inout = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H)
-        inout_ms = time_host(inout, True)
-        # (b) clear + draw as one call (rt_frame.clear): only the frame parameters go up, colour + depth come back
-        e2e_ms = time_host(frame, False)
-        e2e = {"value": px / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms,
-               "h2d_bytes_per_step": C.sizeof(L.RtFrame), "d2h_bytes_per_step": 8 * px,
-               "api": "rt_render_host, rt_frame.clear=1 (FrameBuffer::clear + Renderer::draw in one call), pinned host framebuffer",
-               "inout": {"value": px / inout_ms / 1e3, "ms_per_step": inout_ms, "h2d_bytes_per_step": 8 * px,
-                         "d2h_bytes_per_step": 8 * px, "api": "rt_render_host, in/out framebuffer (raytracing.cpp:17,90-94)"}}
-        # the frame that came back must be the reference's frame (checked against the oracle, outside any timing)
+        def host_clear():   # FrameBuffer::clear() on the host (raytracing.hpp:16-19), main.cpp:197
+            hc.zero_()
+            ht.fill_(float("inf"))
+
+        def host_dirty():
+            hc.fill_(0x5A5A5A5A)
+            ht.fill_(0.25)
+
+        sink = [0]
+
+        def host_blit():    # the viewer reads the colour buffer (SDL_UpdateTexture, main.cpp:238-249)
+            sink[0] += int(hc[::16].sum())
+
+        # correctness first: dirty buffers, the fused clear must overwrite every pixel (checked against the oracle below)
+        host_dirty()
+        L.check(L.lib().rt_render_host(scene.handle, C.byref(frame), C.c_void_p(hc.data_ptr()),
+                                       C.c_void_p(ht.data_ptr()), None, C.byref(dms), C.byref(tms), None))
         chk_c = hc.numpy().view(np.uint32).reshape(H, W).copy()
         chk_t = ht.numpy().reshape(H, W).copy()
+        # (a) clear + draw as one call (rt_frame.clear): only the frame parameters go up, colour + depth come back;
+        #     the caller does not touch the buffers between calls
+        e2e_ms = time_host(frame, lambda: None)
+        blit_ms = time_host(frame, host_blit)
+        dirty_ms = time_host(frame, host_dirty)
+        # (b) the reference's literal in/out contract: the caller clears on the host, depth + colour go up, both come back
+        inout = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+        inout_ms = time_host(inout, host_clear)
+        e2e = {"value": px / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": C.sizeof(L.RtFrame), "d2h_bytes_per_step": 8 * px,
+               "api": "rt_render_host, rt_frame.clear=1 (FrameBuffer::clear + Renderer::draw in one call), pinned host "
+                      "framebuffer left untouched by the CPU between calls",
+               "d2h_floor_ms_at_56GBps": 8 * px / 56e9 * 1e3,
+               "after_cpu_read_of_colour": {"value": px / blit_ms / 1e3, "ms_per_step": blit_ms},
+               "after_cpu_rewrite_of_both_buffers": {"value": px / dirty_ms / 1e3, "ms_per_step": dirty_ms,
+                                                     "note": "dirty CPU cache lines slow the DMA writes"},
+               "inout": {"value": px / inout_ms / 1e3, "ms_per_step": inout_ms, "h2d_bytes_per_step": 8 * px,
+                         "d2h_bytes_per_step": 8 * px,
+                         "api": "rt_render_host, in/out framebuffer cleared on the host before each call (raytracing.cpp:17,90-94)"}}
+        # the frame that came back must be the reference's frame (checked against the oracle, outside any timing)
 
     # ---- workload counters + roofline of the dominant (only) kernel
     # (N > 1: rank 0's share of the frame, the part its kernel launch actually processes)
-    r = scene.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands), want_counters=True)
-    cnt = r["counters"]
+    if orbit:
+        ks = range(0, 64, max(1, 64 // min(64, args.steps)))
+        cnts = [scene.render(rt.make_frame(cams[k][0], cams[k][2], c["projInv"], W, H, bands=bands),
+                             want_counters=True)["counters"] for k in ks]
+        cnt = {k: sum(x[k] for x in cnts) / len(cnts) for k in cnts[0]}
+    else:
+        r = scene.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands), want_counters=True)
+        cnt = r["counters"]
     rays_launch = max(1, cnt["rays"])
     alg_bytes, alg_flops = algorithmic_work(kind, cnt, rays_launch)
     hbm, peak_kind, sm_max = peaks()
     clk = clocks.summary()
     fp32_peak = 148 * 128 * 2 * (clk["sm_mhz"] or sm_max) * 1e6 / 1e12  # TFLOP/s at the clock seen under load
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    scene_bytes = scene.info()["device_bytes"]
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the committed ncu --set full captures
+    if os.path.exists(tp):
+        ent = json.load(open(tp)).get(f"{args.scene}|{args.math}")
+        if ent and world == 1:
+            traffic, traffic_src = ent["dram_bytes_per_launch"], ent["source"]
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "traffic": None, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
                 "kernel_ms": kernel_ms, "kernel_ms_warm_l2": kernel_ms_warm,
                 "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_flops_per_launch": alg_flops,
                 "rays_per_launch": rays_launch,
                 "fp32": {"achieved_tflops": alg_flops / (kernel_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                          "frac": alg_flops / (kernel_ms * 1e-3) / 1e12 / fp32_peak},
-                "note": "scene fits in L2: the operative bounds are cached-gather latency and the FP32 pipe, see DESIGN.md"}
+                "note": ("scene fits in L2: the operative bounds are cached-gather latency and instruction issue, see DESIGN.md"
+                         if scene_bytes < (100 << 20) else
+                         "scene exceeds L2: gathers miss to HBM in 32-byte sectors, see DESIGN.md")}
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "reference scene file (fixture copy), viewer start camera",
         "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal",
-                   "math": args.math, "sched": args.sched, "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
+                   "math": args.math, "sched": args.sched, "grid_layout": args.grid_layout,
+                   "scene_bytes": scene.info()["device_bytes"], "scene_build_s": round(t_build, 3), "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
                    "partition": "whole frame" if world == 1 else
                    f"{band_rows}-row bands interleaved over {world} GPUs, " +
                    ("tiles stored by the render kernel into rank 0's framebuffer over NVLink (CUDA IPC peer mapping)"
@@ -424,7 +495,7 @@ def run_cuda(args):
             line["parity"] = d
     if e2e is not None:
         line["e2e"] = e2e
-        line["cpu_baseline"] = cpu_baseline(g, scene_name, c, W, H)
+        line["cpu_baseline"] = cpu_baseline(g, scene_name, c, W, H, orbit=orbit)
         # correctness of what was timed: the e2e frame against the oracle port (bit-exact in exact mode)
         want = oracle_frame(g, scene_name, c, W, H)
         if want is not None:
@@ -447,6 +518,7 @@ def main():
     ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=("exact", "fast"))
     ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    ap.add_argument("--grid-layout", default="auto", choices=("auto", "linear", "bricks"))
     ap.add_argument("--gather", default="p2p", choices=("p2p", "nccl"),
                     help="N > 1: how tiles reach rank 0 (fused peer stores, or an NCCL send/recv gather)")
     args = ap.parse_args()

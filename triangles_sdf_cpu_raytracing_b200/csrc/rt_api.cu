@@ -3,6 +3,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <mutex>
@@ -344,6 +345,7 @@ int make_frame(const rt_frame *f, FrameDev &d) {
   std::memcpy(d.proj_inv, f->proj_inv, sizeof d.proj_inv);
   d.W = f->width;
   d.H = f->height;
+  d.row0 = 0;
   if (f->band_count <= 1) {
     d.band_rows = f->height;
     d.band_count = 1;
@@ -371,11 +373,22 @@ int make_frame(const rt_frame *f, FrameDev &d) {
   return RT_OK;
 }
 
-// per-scene-type default scheduling, chosen by measurement (DESIGN.md "scheduling")
+// tuning knobs for measurement runs (read once): RT_TILE_BLOCK = threads per block of the tiles kernel,
+// RT_HOST_CHUNKS = row chunks of rt_render_host's copy/render pipeline.  Unset = the measured defaults.
+int env_int(const char *name) {
+  const char *v = std::getenv(name);
+  return v ? std::atoi(v) : 0;
+}
+const int g_env_tile_block = env_int("RT_TILE_BLOCK");
+const int g_env_host_chunks = env_int("RT_HOST_CHUNKS");
+
+// per-scene-type default scheduling, chosen by measurement (profiles/r1_tune.txt): the octree
+// descent has the most uneven per-warp cost and gains from persistent warps pulling tiles; the grid marcher, the BVH
+// traversal (with 128-thread blocks) and the tiny brute-force scenes are as fast or faster as plain tiles.
 int resolve_sched(const rt_scene *s) {
   int m = g_sched.load();
   if (m != RT_SCHED_AUTO) return m;
-  (void)s;
+  if (s->kind == RT_SCENE_OCTREE) return RT_SCHED_PERSISTENT;
   return RT_SCHED_TILES;
 }
 
@@ -391,6 +404,7 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   a.counters = reinterpret_cast<unsigned long long *>(counters_dev);
   rt_scene *ms = const_cast<rt_scene *>(scene);
   a.tile_counter = scene->tile_counters + (ms->next_counter.fetch_add(1) % N_TILE_COUNTERS);
+  a.tile_block = g_env_tile_block;
   const int sched = resolve_sched(scene);
   cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, scene->sm_count, st)
                                                   : exact::launch_render(a, sched, scene->sm_count, st);
@@ -457,24 +471,43 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   // chunk overlap the kernel of the next, so the call costs ~max(copy time, kernel time), not their sum.
   const bool whole = fd.band_count <= 1;
   const bool need_upload = !(fd.clear && whole);  // a fused clear of the whole frame overwrites every pixel
+  // Chunk boundaries grow geometrically: the kernel outruns PCIe (~17 Grays/s vs 56 GB/s / 8 B = 7 Gpixels/s), so a
+  // small first chunk gets the first download going after a few microseconds and each later, larger chunk is rendered
+  // while the previous one is still on the wire.  RT_HOST_CHUNKS=n forces n equal chunks (measurement sweeps).
+  uint32_t bounds[18];
   uint32_t n_chunks = 1;
-  if (whole && fd.H >= 64) n_chunks = std::min<uint32_t>(16u, std::max<uint32_t>(1u, fd.H / 128u));
-  const uint32_t chunk_rows = (fd.H + n_chunks - 1) / n_chunks;
+  bounds[0] = 0;
+  bounds[1] = fd.H;
+  if (whole && fd.H >= 64) {
+    if (g_env_host_chunks > 0) {
+      n_chunks = std::min<uint32_t>(16u, std::min<uint32_t>(fd.H, (uint32_t)g_env_host_chunks));
+      const uint32_t rows = (fd.H + n_chunks - 1) / n_chunks;
+      for (uint32_t k = 1; k <= n_chunks; ++k) bounds[k] = std::min(fd.H, k * rows);
+    } else {
+      uint32_t rows = std::max<uint32_t>(16u, fd.H / 40u), r = 0;
+      n_chunks = 0;
+      while (r < fd.H && n_chunks < 15) {
+        r = std::min(fd.H, r + rows);
+        if (fd.H - r < rows) r = fd.H;  // fold a short remainder into this chunk
+        bounds[++n_chunks] = r;
+        rows *= 2;
+      }
+      if (r < fd.H) bounds[++n_chunks] = fd.H;
+    }
+  }
   RT_CUDA(cudaEventRecord(s->ev[0], st));
   if (prim && need_upload) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));  // rows not rendered: MISS
   if (counters) RT_CUDA(cudaMemsetAsync(s->h_cnt, 0, sizeof(rt_counters), st));
   RT_CUDA(cudaEventRecord(s->ev[1], st));
   RT_CUDA(cudaStreamWaitEvent(s->h_up, s->ev[0], 0));
   for (uint32_t k = 0; k < n_chunks; ++k) {
-    const uint32_t r0 = k * chunk_rows, r1 = std::min(fd.H, r0 + chunk_rows);
-    if (r0 >= r1) break;
+    const uint32_t r0 = bounds[k], r1 = bounds[k + 1];
+    if (r0 >= r1) continue;
     const size_t off = (size_t)r0 * fd.W, cbytes = (size_t)(r1 - r0) * fd.W * 4;
     FrameDev fk = fd;
-    if (n_chunks > 1) {  // chunk k = band k of a (chunk_rows, n_chunks) partition
-      fk.band_rows = chunk_rows;
-      fk.band_count = n_chunks;
-      fk.band_index = k;
-      fk.rows_here = chunk_rows;
+    if (n_chunks > 1) {  // rows [r0, r1) of the frame
+      fk.row0 = r0;
+      fk.rows_here = r1 - r0;
     }
     if (need_upload) {
       const size_t uoff = n_chunks > 1 ? off : 0, ubytes = n_chunks > 1 ? cbytes : bytes;

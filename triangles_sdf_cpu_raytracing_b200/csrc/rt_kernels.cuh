@@ -171,11 +171,36 @@ __device__ __forceinline__ void flush_counters(const Counters &c, unsigned long 
   }
 }
 
-// stage the whole triangle list in shared memory (brute-force scenes; 48 B per triangle, float4 loads)
+// Stage the whole triangle list in shared memory (brute-force scenes; 48 B per triangle = 3 x float4).
+// The list is one contiguous, 16-byte-aligned run of n_tris * 48 bytes, i.e. tile-regular: one elected thread
+// issues a single TMA bulk copy (cp.async.bulk global -> shared, SASS UBLKCP) that completes on an mbarrier; every
+// thread of the block then waits on the barrier's phase.  No thread spends load/store instructions on the copy.
 __device__ __forceinline__ void stage_triangles(const MeshDev &m, float4 *smemTris) {
-  const float4 *src = reinterpret_cast<const float4 *>(m.tris);
-  for (uint32_t i = threadIdx.x; i < 3 * m.n_tris; i += blockDim.x) smemTris[i] = __ldg(src + i);
+  __shared__ __align__(8) unsigned long long mbar;
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
+  const uint32_t dst = (uint32_t)__cvta_generic_to_shared(smemTris);
+  const uint32_t bytes = m.n_tris * (uint32_t)sizeof(TriDev);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(m.tris), "r"(bytes), "r"(bar)
+                 : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(0)
+        : "memory");
+  }
 }
 
 // one pixel: memory row `row` (0 = top), column x
@@ -205,19 +230,30 @@ __device__ __forceinline__ void shade_pixel(const RenderArgs &a, const float4 *s
 
 // virtual row v (0 .. rows_here) of this call -> memory row of the frame (interleaved bands, rt_frame)
 __device__ __forceinline__ uint32_t band_row(const FrameDev &f, uint32_t v) {
-  if (f.band_count <= 1u) return v;
+  if (f.band_count <= 1u) return f.row0 + v;
   const uint32_t b = v / f.band_rows, r = v - b * f.band_rows;
   return (b * f.band_count + f.band_index) * f.band_rows + r;
 }
 
+// Rows of tiles are handed out from the middle of the call's rows outwards (0 -> mid, 1 -> mid-1, 2 -> mid+1, ...):
+// the model sits mid-screen, so the long marches / deep traversals start first and the cheap box-miss tiles at the
+// top and bottom of the frame fill the tail of the launch instead of one late heavy tile stretching it.
+__device__ __forceinline__ uint32_t centre_out(uint32_t i, uint32_t n) {
+  const uint32_t mid = n >> 1, k = i >> 1;
+  return (i & 1u) ? mid - 1u - k : mid + k;
+}
+
 // ---- RT_SCHED_TILES: one thread per pixel -------------------------------------------------------------------
-template <int KIND, bool COUNT, bool SECONDARY>
-__global__ void __launch_bounds__(BLOCK_THREADS) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
+// A block is WX x WY warp tiles.  An SM releases a block's registers and warp slots only when its LAST warp retires,
+// so with long-tailed per-ray costs (one grazing ray marching 100+ steps) big blocks strand resident-warp slots
+// behind their slowest warp; the block shape per scene kind is chosen by measurement.
+template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY>
+__global__ void __launch_bounds__(32 * WX * WY) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
   if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t x = blockIdx.x * 32u + (warp & 3u) * TILE_W + (lane & 7u);
-  const uint32_t v = blockIdx.y * 8u + (warp >> 2) * TILE_H + (lane >> 3);
+  const uint32_t x = (blockIdx.x * WX + warp % WX) * TILE_W + (lane & 7u);
+  const uint32_t v = (centre_out(blockIdx.y, gridDim.y) * WY + warp / WX) * TILE_H + (lane >> 3);
   Counters cnt = {};
   if (x < a.frame.W && v < a.frame.rows_here) {
     const uint32_t row = band_row(a.frame, v);
@@ -243,7 +279,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS) render_persistent_kernel(const 
     if (lane == 0) tile = atomicAdd(a.tile_counter, 1u);
     tile = __shfl_sync(0xffffffffu, tile, 0);
     if (tile >= nTiles) break;
-    const uint32_t ty = tile / tilesX, tx = tile - ty * tilesX;
+    const uint32_t tyi = tile / tilesX, tx = tile - tyi * tilesX, ty = centre_out(tyi, tilesY);
     const uint32_t x = tx * TILE_W + (lane & 7u), v = ty * TILE_H + (lane >> 3);
     if (x < a.frame.W && v < a.frame.rows_here) {
       const uint32_t row = band_row(a.frame, v);
@@ -281,6 +317,15 @@ static inline int kind_of(const SceneDev &s) {
   return s.mesh.brute ? KIND_BRUTE : KIND_BVH;
 }
 
+template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY>
+static cudaError_t launch_tiles_shape(const RenderArgs &a, size_t smem, cudaStream_t st) {
+  auto kern = render_tiles_kernel<KIND, COUNT, SECONDARY, WX, WY>;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  dim3 grid((a.frame.W + TILE_W * WX - 1u) / (TILE_W * WX), (a.frame.rows_here + TILE_H * WY - 1u) / (TILE_H * WY));
+  kern<<<grid, 32 * WX * WY, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
 template <int KIND, bool COUNT, bool SECONDARY>
 static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count, cudaStream_t st) {
   const size_t smem = (KIND == KIND_BRUTE) ? (size_t)a.scene.mesh.n_tris * sizeof(TriDev) : 0;
@@ -295,10 +340,18 @@ static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count,
     if (e != cudaSuccess) return e;
     kern<<<dim3((unsigned)(sm_count * perSm)), BLOCK_THREADS, smem, st>>>(a);
   } else {
-    auto kern = render_tiles_kernel<KIND, COUNT, SECONDARY>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 7u) / 8u);
-    kern<<<grid, BLOCK_THREADS, smem, st>>>(a);
+    // Block shape.  Measured on B200 (profiles/r1_tune.txt): 128 threads (2 x 2 warp tiles) is the fastest shape for
+    // the grid, octree and BVH kernels (256 strands warp slots behind a block's slowest warp, 32/64 lose L1 reuse
+    // between neighbouring tiles); the brute-force kernel stages its triangles per block and keeps 256.
+    // a.tile_block (RT_TILE_BLOCK) overrides it for sweeps; only the plain primary-ray kernels have every shape.
+    const int tb = a.tile_block;
+    if (KIND == KIND_BRUTE) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
+    if (!COUNT && !SECONDARY) {
+      if (tb == 32) return launch_tiles_shape<KIND, false, false, 1, 1>(a, smem, st);
+      if (tb == 64) return launch_tiles_shape<KIND, false, false, 2, 1>(a, smem, st);
+      if (tb == 256) return launch_tiles_shape<KIND, false, false, 4, 2>(a, smem, st);
+    }
+    return launch_tiles_shape<KIND, COUNT, SECONDARY, 2, 2>(a, smem, st);
   }
   return cudaGetLastError();
 }

@@ -81,6 +81,7 @@ struct FrameDev {
   uint32_t W, H;
   uint32_t band_rows, band_count, band_index;
   uint32_t rows_here;  // number of memory rows this call renders
+  uint32_t row0;       // whole-frame calls (band_count <= 1): first memory row (row chunks of rt_render_host)
   int32_t mode;
   float light[3];
   int32_t shadows, reflections, has_plane;
@@ -98,6 +99,7 @@ struct RenderArgs {
   uint32_t *prim;
   unsigned long long *counters;  // rt_counters as 9 x u64, or null
   uint32_t *tile_counter;        // persistent scheduling: next tile to hand out
+  int32_t tile_block;            // RT_SCHED_TILES: threads per block (32, 64, 128, 256)
 };
 
 struct RayArgs {

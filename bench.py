@@ -247,7 +247,7 @@ def run_cuda(args):
     scene = util.cuda_scene(g, scene_name, **layout_kw)
     t_build = time.perf_counter() - t_build
     kind = {0: "grid", 1: "octree", 2: "mesh"}[scene.kind]
-    band_rows = 32
+    band_rows = args.band_rows
     bands = (band_rows, world, rank) if world > 1 else None
     # FrameBuffer::clear (raytracing.hpp:16-19) is fused into the render launch: one kernel writes every pixel once
     frame = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, bands=bands, clear=True)
@@ -518,6 +518,8 @@ def main():
     ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=("exact", "fast"))
     ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    ap.add_argument("--band-rows", type=int, default=8,
+                    help="N > 1: rows per interleaved band (a multiple of the 8-row block height)")
     ap.add_argument("--grid-layout", default="auto", choices=("auto", "linear", "bricks"))
     ap.add_argument("--gather", default="p2p", choices=("p2p", "nccl"),
                     help="N > 1: how tiles reach rank 0 (fused peer stores, or an NCCL send/recv gather)")

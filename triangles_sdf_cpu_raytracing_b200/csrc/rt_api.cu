@@ -267,7 +267,7 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
 }
 
 // ---------------------------------------------------------------------------------------------- mesh
-static int finish_mesh(HostBvh &h, bool brute, rt_scene **out) {
+static int finish_mesh(HostBvh &h, bool brute, bool literal_order, rt_scene **out) {
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
   if (rc) return rc;
@@ -277,6 +277,7 @@ static int finish_mesh(HostBvh &h, bool brute, rt_scene **out) {
   m.n_tris = (uint32_t)h.tris.size();
   m.n_nodes = (uint32_t)h.nodes.size();
   m.brute = brute ? 1u : 0u;
+  m.literal_order = literal_order ? 1u : 0u;
   for (int a = 0; a < 3; ++a) {
     s->bbox_min[a] = h.bbox_min[a];
     s->bbox_max[a] = h.bbox_max[a];
@@ -298,7 +299,7 @@ int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *i
   HostBvh h;
   std::string err;
   if (!build_bvh8(vpos4, n_verts, indices, n_indices, accel == RT_MESH_BRUTE, h, err)) return fail(RT_ERR_INVALID, err);
-  return finish_mesh(h, accel == RT_MESH_BRUTE, out);
+  return finish_mesh(h, accel == RT_MESH_BRUTE, false, out);
 }
 
 int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices_bvh, uint32_t n_indices,
@@ -309,7 +310,7 @@ int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32
   if (!import_reference_bvh(vpos4, n_verts, indices_bvh, n_indices, nodes, n_nodes, node_bytes, prim_of_permuted, h,
                             err))
     return fail(RT_ERR_INVALID, err);
-  return finish_mesh(h, false, out);
+  return finish_mesh(h, false, true, out);
 }
 
 void rt_scene_destroy(rt_scene *scene) { scene_free(scene); }

@@ -299,16 +299,26 @@ __device__ __forceinline__ V3 oct_node_normal(const float (&v)[8], V3 bmin, floa
 
 // SDFOctree::intersectLeaf, octree_raytracing.cpp:122-164, for a leaf that survived the value culls.
 // On a hit the sample point is returned in `pHit`; the caller evaluates the normal once the traversal is over.
+// KNOWN_INSIDE: the caller reached this leaf through the closed-form child list (oct_children_fast), i.e. the ISPC
+// slab test of the leaf box succeeded with finite, NaN-free plane distances and tNear > 0.  Then
+// BBox3f::Intersection cannot reject it (its t2 is the same tMax with every term scaled by 1.00000024 >= the slab
+// test's, its t1 the same max of the near-plane distances) and t1 reduces to max(near-plane distances, tNear): the
+// same products (plane - o) * inv on the same operands, selected by the sign of 1/dir as LiteMath.h:2011-2016 does.
 template <bool COUNT>
-__device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 bmin, float ext, V3 o, V3 d, V3 inv,
-                                         float tNear, float tFar, Hit &r, V3 &pHit, Counters &cnt) {
+__device__ __forceinline__ bool oct_leaf(const OctreeDev &oc, uint32_t node, V3 bmin, float ext, float invExt, V3 o,
+                                         V3 d, V3 inv, float tNear, float tFar, bool KNOWN_INSIDE, Hit &r, V3 &pHit,
+                                         Counters &cnt) {
   V3 bmax = mk3(bmin.x + ext, bmin.y + ext, bmin.z + ext);
   float t1, t2;
-  bbox_intersection(bmin, bmax, o, inv, tNear, tFar, t1, t2);
-  if (t1 > t2) return false;
+  if (KNOWN_INSIDE) {
+    const float nx = inv.x < 0 ? bmax.x : bmin.x, ny = inv.y < 0 ? bmax.y : bmin.y, nz = inv.z < 0 ? bmax.z : bmin.z;
+    t1 = fmaxf(fmaxf((nx - o.x) * inv.x, (ny - o.y) * inv.y), fmaxf((nz - o.z) * inv.z, tNear));
+  } else {
+    bbox_intersection(bmin, bmax, o, inv, tNear, tFar, t1, t2);
+    if (t1 > t2) return false;
+  }
   const float4 a = __ldg(oc.values + 2 * (size_t)node), b = __ldg(oc.values + 2 * (size_t)node + 1);
   const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-  const float invExt = 1.0f / ext;
   float t = t1;
   V3 p = along(o, d, t);
   p.x = std_max(p.x, bmin.x); p.y = std_max(p.y, bmin.y); p.z = std_max(p.z, bmin.z);
@@ -417,9 +427,11 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
 // ordered list of the children of the inner node with box (bmin, ext) that the ray visits: up to 8 nibbles,
 // first to visit in the low nibble, bit 3 = valid, bits 0..2 = child id
 __device__ __forceinline__ uint32_t oct_children(V3 bmin, float ext, V3 o, V3 inv, bool finiteInv, bool fastOk,
-                                                 uint32_t nearMask, float tNear, float tFar) {
+                                                 uint32_t nearMask, float tNear, float tFar, bool &closedForm) {
   uint32_t w = 0;
-  if (fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w)) return w;
+  // closedForm: the list came from the closed form, so every child in it passed a NaN-free slab test
+  closedForm = fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w);
+  if (closedForm) return w;
   // literal path: axis-parallel rays, tNear <= 0, exact ties
   float ts[8];
   uint32_t ch[8];
@@ -443,13 +455,14 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   const bool fastOk = finiteInv && inv.x != 0.0f && inv.y != 0.0f && inv.z != 0.0f && tNear > 0.0f && tFar >= tNear;
   const uint32_t nearMask = (inv.x < 0.0f ? 4u : 0u) | (inv.y < 0.0f ? 2u : 0u) | (inv.z < 0.0f ? 1u : 0u);
   V3 hitMin = mk3(0.0f, 0.0f, 0.0f), pHit = hitMin;
-  float hitExt = 0.0f;
+  float hitInvExt = 0.0f;
   const uint32_t rootLink = __ldg(oc.link);
   if (rootLink == OCT_LEAF_SURFACE || rootLink == OCT_LEAF_CULLED) {
     if (COUNT) cnt.oct_leaf++;
     hitMin = mk3(-1.0f, -1.0f, -1.0f);
-    hitExt = 2.0f;
-    if (rootLink == OCT_LEAF_SURFACE) oct_leaf<COUNT>(oc, 0, hitMin, 2.0f, o, d, inv, tNear, tFar, r, pHit, cnt);
+    hitInvExt = 0.5f;
+    if (rootLink == OCT_LEAF_SURFACE)
+      oct_leaf<COUNT>(oc, 0, hitMin, 2.0f, 0.5f, o, d, inv, tNear, tFar, false, r, pHit, cnt);
   } else {
     // Iterate the children of the CURRENT inner node from registers; only stepping into an inner child saves
     // the parent's state (leaf children, the majority of visits, never touch the stack).
@@ -457,11 +470,16 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     uint32_t base[OCT_MAX_DEPTH + 1];  // ... and its childrenOffset
     int level = 0;                     // depth of the current inner node
     V3 bmin = mk3(-1.0f, -1.0f, -1.0f);  // its box: dyadic, so parent/child corners are exact sums
-    float ext = 2.0f;
+    float ext = 2.0f, invExt = 0.5f;   // 1/ext: both powers of two, kept exact by doubling / halving
     unsigned long long path = 0;       // 3 bits per level: child ids on the way down (for stepping back up)
+    uint32_t closedMask = 0;           // bit l: the child list of the level-l node on the path is a closed-form one
     uint32_t cbase = rootLink;
     if (COUNT) cnt.oct_inner++;
-    uint32_t w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar);
+    bool cf;
+    uint32_t w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+    closedMask = cf ? 1u : 0u;
+    // (A "while-while" form, all lanes walking to their next surface leaf before any of them marches, was measured
+    // and rejected: octree6 4K 0.73 -> 0.75 ms, depth-8 stand-in 1.16 -> 1.34 ms; profiles/r1_tune.txt.)
     for (;;) {
       if (w == 0) {
         // ---- back to the parent
@@ -473,6 +491,7 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
         path >>= 3;
         bmin = mk3(bmin.x - ((id & 4u) ? ext : 0.0f), bmin.y - ((id & 2u) ? ext : 0.0f), bmin.z - ((id & 1u) ? ext : 0.0f));
         ext *= 2.0f;
+        invExt *= 0.5f;
         continue;
       }
       const uint32_t id = w & 7u;
@@ -483,10 +502,14 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
       const V3 cmin = mk3(bmin.x + ((id & 4u) ? h : 0.0f), bmin.y + ((id & 2u) ? h : 0.0f), bmin.z + ((id & 1u) ? h : 0.0f));
       if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
         if (COUNT) cnt.oct_leaf++;
-        if (link == OCT_LEAF_SURFACE && oct_leaf<COUNT>(oc, child, cmin, h, o, d, inv, tNear, tFar, r, pHit, cnt)) {
-          hitMin = cmin;
-          hitExt = h;
-          break;  // the first leaf that reports a hit ends the whole descent (octree_raytracing.cpp:188-197)
+        if (link == OCT_LEAF_SURFACE) {
+          const float ih = invExt * 2.0f;
+          if (oct_leaf<COUNT>(oc, child, cmin, h, ih, o, d, inv, tNear, tFar, ((closedMask >> level) & 1u) != 0u, r,
+                              pHit, cnt)) {
+            hitMin = cmin;
+            hitInvExt = ih;
+            break;  // the first leaf that reports a hit ends the whole descent (octree_raytracing.cpp:188-197)
+          }
         }
       } else {
         if (COUNT) cnt.oct_inner++;
@@ -496,8 +519,10 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
         path = (path << 3) | id;
         bmin = cmin;
         ext = h;
+        invExt *= 2.0f;
         cbase = link;
-        w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar);
+        w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+        closedMask = (closedMask & ~(1u << level)) | (cf ? (1u << level) : 0u);
       }
     }
   }
@@ -505,7 +530,7 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     // the hit leaf's normal, evaluated by all lanes that hit together (values are an L1 hit)
     const float4 a = __ldg(oc.values + 2 * (size_t)r.prim), b = __ldg(oc.values + 2 * (size_t)r.prim + 1);
     const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-    r.normal = oct_node_normal(v, hitMin, 1.0f / hitExt, pHit);
+    r.normal = oct_node_normal(v, hitMin, hitInvExt, pHit);
   }
   return r;
 }
@@ -518,11 +543,32 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
 // evaluated at pop time against the best hit so far.  (The recursion culls against the best hit of the
 // enclosing node only; a subtree it visits and we skip starts behind the current best hit, so it cannot
 // change the closest hit — DESIGN.md "BVH culling".)  Ties keep the first hit in visit order (strict '>').
+// Fast inner-node path (our own trees, all three 1/dir finite and non-zero, tNear > 0):
+//  * the near / far plane of every child on each axis is picked by the SIGN of 1/dir instead of min/max of the two
+//    plane distances: lo <= hi and rounding is monotonic, so min((lo-o)*inv, (hi-o)*inv) IS the near-plane product,
+//    bit for bit.  The sign is a per-ray constant, so it only changes which 32-byte run of the SoA node is loaded.
+//  * children are ordered by a single 32-bit key = entry distance with its 3 low mantissa bits replaced by the
+//    child's lane (entry distances are >= tNear > 0, so their bit patterns order like the floats).  Closest-hit
+//    results do not depend on the visit order (only on which triangles get tested, and the pop-time cull below uses a
+//    key that is <= the exact entry distance, i.e. it culls a subset of what the exact value would); only exact-t
+//    ties between triangles can resolve differently, and those already depend on the tree.
+// Trees imported from the reference (rt_scene_create_mesh_bvh8) keep the literal slab test + sort8 network so
+// that their visit order, and with it every tie, is the reference's own.
+__device__ __forceinline__ void key_cswap(uint32_t &a, uint32_t &b) {
+  const uint32_t lo = min(a, b), hi = max(a, b);
+  a = lo;
+  b = hi;
+}
+
 template <bool COUNT>
 __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
   const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   const bool finiteInv = isfinite(inv.x) && isfinite(inv.y) && isfinite(inv.z);
+  const bool fastNode = finiteInv && !m.literal_order && inv.x != 0.0f && inv.y != 0.0f && inv.z != 0.0f &&
+                        tNear > 0.0f;
+  // float4 index inside the 224-byte node of the near / far plane runs (lo.x 0, lo.y 2, lo.z 4, hi.x 6, hi.y 8, hi.z 10)
+  const uint32_t nx4 = inv.x < 0.0f ? 6u : 0u, ny4 = inv.y < 0.0f ? 8u : 2u, nz4 = inv.z < 0.0f ? 10u : 4u;
   uint32_t stackRef[BVH_STACK];
   float stackT[BVH_STACK];
   int sp = 0;
@@ -532,6 +578,45 @@ __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float
     if (!(ref & BVH_LEAF_BIT)) {
       if (COUNT) cnt.bvh_inner++;
       const float4 *n4 = reinterpret_cast<const float4 *>(m.nodes + ref);
+      if (fastNode) {
+        uint32_t key[8];
+#pragma unroll
+        for (int hlf = 0; hlf < 2; ++hlf) {
+          const float4 ax = __ldg(n4 + nx4 + hlf), bx = __ldg(n4 + (6u - nx4) + hlf);
+          const float4 ay = __ldg(n4 + ny4 + hlf), by = __ldg(n4 + (10u - ny4) + hlf);
+          const float4 az = __ldg(n4 + nz4 + hlf), bz = __ldg(n4 + (14u - nz4) + hlf);
+          const float nX[4] = {ax.x, ax.y, ax.z, ax.w}, fX[4] = {bx.x, bx.y, bx.z, bx.w};
+          const float nY[4] = {ay.x, ay.y, ay.z, ay.w}, fY[4] = {by.x, by.y, by.z, by.w};
+          const float nZ[4] = {az.x, az.y, az.z, az.w}, fZ[4] = {bz.x, bz.y, bz.z, bz.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float tnx = (nX[j] - o.x) * inv.x, tny = (nY[j] - o.y) * inv.y, tnz = (nZ[j] - o.z) * inv.z;
+            const float tfx = (fX[j] - o.x) * inv.x, tfy = (fY[j] - o.y) * inv.y, tfz = (fZ[j] - o.z) * inv.z;
+            const float tMin = fmaxf(fmaxf(tnx, fmaxf(tny, tnz)), tNear);
+            const float tMax = fminf(fminf(tfx, fminf(tfy, tfz)), tFar);
+            // unused lanes hold the box (+inf, -inf) and miss here; tMin >= tNear > 0
+            key[4 * hlf + j] = (tMax < 0 || tMin > tMax) ? 0xFFFFFFFFu
+                                                         : ((__float_as_uint(tMin) & ~7u) | (uint32_t)(4 * hlf + j));
+          }
+        }
+        // the 19-comparator network of raytracing.hpp:188-213 on the packed keys (misses sort last)
+        key_cswap(key[0], key[1]); key_cswap(key[2], key[3]); key_cswap(key[4], key[5]); key_cswap(key[6], key[7]);
+        key_cswap(key[0], key[2]); key_cswap(key[1], key[3]); key_cswap(key[4], key[6]); key_cswap(key[5], key[7]);
+        key_cswap(key[1], key[2]); key_cswap(key[5], key[6]); key_cswap(key[0], key[4]); key_cswap(key[3], key[7]);
+        key_cswap(key[1], key[5]); key_cswap(key[2], key[6]);
+        key_cswap(key[1], key[4]); key_cswap(key[3], key[6]);
+        key_cswap(key[2], key[4]); key_cswap(key[3], key[5]);
+        key_cswap(key[3], key[4]);
+        const uint32_t *childWord = reinterpret_cast<const uint32_t *>(n4 + 12);
+#pragma unroll
+        for (int i = 7; i >= 0; --i) {
+          if (key[i] != 0xFFFFFFFFu) {  // far-to-near pushes: the nearest child pops first
+            stackRef[sp] = __ldg(childWord + (key[i] & 7u));
+            stackT[sp] = __uint_as_float(key[i] & ~7u);
+            ++sp;
+          }
+        }
+      } else {
       float b[48];
 #pragma unroll
       for (int i = 0; i < 12; ++i) {
@@ -564,6 +649,7 @@ __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float
           stackT[sp] = t[i];
           ++sp;
         }
+      }
       }
     } else {
       if (COUNT) cnt.bvh_leaf++;

@@ -64,6 +64,7 @@ struct MeshDev {
   const TriDev *tris;
   uint32_t n_nodes, n_tris;
   uint32_t brute;  // 1: no BVH, all triangles are tested from shared memory
+  uint32_t literal_order;  // 1: tree imported from the reference: literal slab test + sort8 visit order
 };
 
 struct SceneDev {

@@ -242,8 +242,12 @@ def run_cuda(args):
     g, scene_name, c, W, H = load_workload(args.scene)
     t_build = time.perf_counter()
     layout_kw = {}
-    if args.grid_layout != "auto":
+    arrays = g.scene_arrays(scene_name)  # (stand-ins are generated here, outside the build stopwatch)
+    t_build = time.perf_counter()
+    if "values" in arrays and args.grid_layout != "auto":
         layout_kw = {"layout": {"linear": rt.GRID_LINEAR, "bricks": rt.GRID_BRICKS}[args.grid_layout]}
+    if "vpos4" in arrays and args.mesh_accel != "auto":
+        layout_kw = {"accel": {"host": rt.MESH_BVH8, "lbvh_gpu": rt.MESH_LBVH_GPU}[args.mesh_accel]}
     scene = util.cuda_scene(g, scene_name, **layout_kw)
     t_build = time.perf_counter() - t_build
     kind = {0: "grid", 1: "octree", 2: "mesh"}[scene.kind]
@@ -478,7 +482,8 @@ def run_cuda(args):
         "vs_baseline": None, "dtype": "f32", "data": "reference scene file (fixture copy), viewer start camera",
         "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal",
                    "math": args.math, "sched": args.sched, "grid_layout": args.grid_layout,
-                   "scene_bytes": scene.info()["device_bytes"], "scene_build_s": round(t_build, 3), "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
+                   "scene_bytes": scene.info()["device_bytes"], "scene_build_s": round(t_build, 3),
+                   "mesh_accel": args.mesh_accel, "mesh": scene.mesh_stats() if kind == "mesh" else None, "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
                    "partition": "whole frame" if world == 1 else
                    f"{band_rows}-row bands interleaved over {world} GPUs, " +
                    ("tiles stored by the render kernel into rank 0's framebuffer over NVLink (CUDA IPC peer mapping)"
@@ -518,6 +523,8 @@ def main():
     ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=("exact", "fast"))
     ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    ap.add_argument("--mesh-accel", default="auto", choices=("auto", "host", "lbvh_gpu"),
+                    help="who builds the 8-wide BVH: the host (binned SAH) or the device (linear BVH)")
     ap.add_argument("--band-rows", type=int, default=8,
                     help="N > 1: rows per interleaved band (a multiple of the 8-row block height)")
     ap.add_argument("--grid-layout", default="auto", choices=("auto", "linear", "bricks"))

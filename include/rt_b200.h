@@ -58,7 +58,12 @@ typedef enum rt_grid_layout { RT_GRID_AUTO = 0, RT_GRID_LINEAR = 1, RT_GRID_BRIC
 
 /* Triangle-scene traversal. BVH8 = our 8-wide BVH; BRUTE = every ray tests every triangle from shared
  * memory (the loop ray_pack.ispc:167-202 describes; only for small meshes). */
-typedef enum rt_mesh_accel { RT_MESH_AUTO = 0, RT_MESH_BVH8 = 1, RT_MESH_BRUTE = 2 } rt_mesh_accel;
+typedef enum rt_mesh_accel {
+  RT_MESH_AUTO = 0,
+  RT_MESH_BVH8 = 1,     /* binned-SAH tree built on the host, collapsed to 8-wide */
+  RT_MESH_BRUTE = 2,
+  RT_MESH_LBVH_GPU = 3  /* linear BVH (Morton order) built on the device, collapsed to 8-wide: milliseconds for 10^6 triangles */
+} rt_mesh_accel;
 
 typedef enum rt_scene_kind { RT_SCENE_GRID = 0, RT_SCENE_OCTREE = 1, RT_SCENE_MESH = 2 } rt_scene_kind;
 
@@ -123,6 +128,9 @@ int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *i
 int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices_bvh, uint32_t n_indices,
                               const void *nodes, uint32_t n_nodes, uint32_t node_bytes,
                               const uint32_t *prim_of_permuted, rt_scene **out);
+/* mesh scenes: size of the tree and, for RT_MESH_LBVH_GPU, the device time of its construction (0 otherwise).
+ * Any output pointer may be NULL. */
+int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tris, float *device_build_ms);
 void rt_scene_destroy(rt_scene *scene);
 int rt_scene_kind_of(const rt_scene *scene);             /* rt_scene_kind */
 int rt_scene_device(const rt_scene *scene);

@@ -80,12 +80,14 @@ def test_grid_brick_layout_is_bit_exact():
         assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
 
 
-@pytest.mark.parametrize("accel", (rt.MESH_BVH8, rt.MESH_BRUTE))
+@pytest.mark.parametrize("accel", (rt.MESH_BVH8, rt.MESH_BRUTE, rt.MESH_LBVH_GPU))
 @pytest.mark.parametrize("key", MESH_CASES)
 def test_mesh_scenes_vs_reference(key, accel):
     c = G.case(key)
     if accel == rt.MESH_BRUTE and c["scene"] != "cube":
         pytest.skip("brute force is for small meshes")
+    if accel == rt.MESH_LBVH_GPU and c["scene"] == "cube":
+        pytest.skip("12 triangles: nothing for the device builder to build")
     s = scene(c["scene"], accel=accel)
     r = s.render(_frame(c), want_prim=True)
     # closest hit does not depend on the tree: depth and colour are bit-identical, prim ids may differ on exact ties
@@ -96,6 +98,33 @@ def test_mesh_scenes_vs_reference(key, accel):
     assert util.rgb_max_diff(r["color"][~same] >> 24, c["color_normal"][~same] >> 24) == 0  # alpha: hit everywhere
     r = s.render(_frame(c, mode=rt.SHADE_LAMBERT))
     assert np.array_equal(r["color"][same], c["color_lambert"][same])
+
+
+def test_device_built_bvh_structure_and_large_mesh():
+    """RT_MESH_LBVH_GPU: the tree built on the device renders the same closest hits as the host-built
+    one on the 1.1 M-triangle stand-in, and reports its size / build time."""
+    a = G.scene_arrays("stanford-bunny_s2")
+    host = rt.TriangleMesh(a["vpos4"], a["indices"], accel=rt.MESH_BVH8)
+    dev = rt.TriangleMesh(a["vpos4"], a["indices"], accel=rt.MESH_LBVH_GPU)
+    st = dev.mesh_stats()
+    assert st["n_tris"] == a["indices"].size // 3 and 0 < st["n_nodes"] < st["n_tris"] // 2
+    assert 0.0 < st["device_build_ms"] < 200.0
+    assert host.mesh_stats()["device_build_ms"] == 0.0
+    assert np.allclose(dev.info()["bbox_min"], host.info()["bbox_min"]) and np.allclose(dev.info()["bbox_max"], host.info()["bbox_max"])
+    c = G.case("stanford-bunny|default|160x90")
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], 1920, 1080)
+    rh, rd = host.render(f, want_prim=True), dev.render(f, want_prim=True)
+    assert util.same_bits(rh["t"], rd["t"])
+    same = rh["prim"] == rd["prim"]
+    assert (~same).sum() <= 0.001 * same.size          # exact-t ties between neighbouring triangles only
+    assert np.array_equal(rh["color"][same], rd["color"][same])
+    # malformed input is rejected, not read out of bounds
+    bad = a["indices"].copy()
+    bad[5] = a["vpos4"].shape[0] + 7
+    with pytest.raises(rt.RtError):
+        rt.TriangleMesh(a["vpos4"], bad, accel=rt.MESH_LBVH_GPU)
+    host.destroy()
+    dev.destroy()
 
 
 def test_reference_built_bvh_is_traversed_identically():

@@ -12,7 +12,7 @@ SHADE_NORMAL, SHADE_LAMBERT, SHADE_COLOR = 0, 1, 2
 MATH_EXACT, MATH_FAST = 0, 1
 SCHED_AUTO, SCHED_TILES, SCHED_PERSISTENT = 0, 1, 2
 GRID_AUTO, GRID_LINEAR, GRID_BRICKS = 0, 1, 2
-MESH_AUTO, MESH_BVH8, MESH_BRUTE = 0, 1, 2
+MESH_AUTO, MESH_BVH8, MESH_BRUTE, MESH_LBVH_GPU = 0, 1, 2, 3
 SCENE_GRID, SCENE_OCTREE, SCENE_MESH = 0, 1, 2
 PRIM_MISS = 0xFFFFFFFF
 PRIM_PLANE = 0xFFFFFFFE
@@ -50,6 +50,7 @@ SIGNATURES = {
     "rt_scene_create_octree": (_i, [_vp, _u32, _pp]),
     "rt_scene_create_mesh": (_i, [_vp, _u32, _vp, _u32, _i, _pp]),
     "rt_scene_create_mesh_bvh8": (_i, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _vp, _pp]),
+    "rt_scene_mesh_stats": (_i, [_vp, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_f)]),
     "rt_scene_destroy": (None, [_vp]),
     "rt_scene_kind_of": (_i, [_vp]),
     "rt_scene_device": (_i, [_vp]),

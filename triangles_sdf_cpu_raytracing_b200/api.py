@@ -67,6 +67,12 @@ class Scene:
         L.check(L.lib().rt_scene_info(self._h, C.byref(b), lo, hi))
         return dict(device_bytes=int(b.value), bbox_min=np.array(lo[:], np.float32), bbox_max=np.array(hi[:], np.float32))
 
+    def mesh_stats(self):
+        """Mesh scenes: dict(n_nodes, n_tris, device_build_ms) (device_build_ms is 0 for host-built trees)."""
+        n, t, ms = C.c_uint32(), C.c_uint32(), C.c_float()
+        L.check(L.lib().rt_scene_mesh_stats(self._h, C.byref(n), C.byref(t), C.byref(ms)))
+        return dict(n_nodes=int(n.value), n_tris=int(t.value), device_build_ms=float(ms.value))
+
     # ---- Renderer::draw with host framebuffers
     def render(self, frame: L.RtFrame, color=None, t=None, want_prim=False, want_counters=False):
         """-> dict(color [H,W] u32, t [H,W] f32, prim or None, device_ms, total_ms, counters or None).

@@ -29,4 +29,18 @@ bool import_reference_bvh(const float *vpos4, uint32_t n_verts, const uint32_t *
                           const void *nodes, uint32_t n_nodes, uint32_t node_bytes, const uint32_t *prim_of_permuted,
                           HostBvh &out, std::string &err);
 
+// The same tree built on the device (bvh_gpu.cu): linear BVH over 63-bit Morton codes, collapsed to 8-wide.
+// nodes / tris are cudaMalloc'ed on the current device and owned by the caller on success.
+struct DeviceBvh {
+  BvhNode *nodes = nullptr;
+  TriDev *tris = nullptr;
+  uint32_t n_nodes = 0, n_tris = 0;
+  float bbox_min[3] = {0, 0, 0}, bbox_max[3] = {0, 0, 0};
+  int stack_need = 0;
+  int levels = 0;        // depth of the 8-wide tree
+  float build_ms = 0.0f; // device time of the build kernels (excluding the upload of vertices / indices)
+};
+bool build_bvh8_device(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, DeviceBvh &out,
+                       std::string &err);
+
 }  // namespace rt

@@ -61,6 +61,7 @@ struct rt_scene {
   std::vector<void *> allocs;
   uint64_t bytes = 0;
   float bbox_min[3] = {-1, -1, -1}, bbox_max[3] = {1, 1, 1};
+  float build_ms = 0.0f;              // device time of an on-device BVH build
   uint32_t *tile_counters = nullptr;  // ring, one per in-flight persistent launch
   std::atomic<uint32_t> next_counter{0};
   // framebuffer cache of rt_render_host
@@ -291,8 +292,43 @@ static int finish_mesh(HostBvh &h, bool brute, bool literal_order, rt_scene **ou
 
 int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, int accel,
                          rt_scene **out) {
-  if (accel < RT_MESH_AUTO || accel > RT_MESH_BRUTE) return fail(RT_ERR_INVALID, "unknown mesh accel");
+  if (accel < RT_MESH_AUTO || accel > RT_MESH_LBVH_GPU) return fail(RT_ERR_INVALID, "unknown mesh accel");
   const uint32_t nTri = n_indices / 3;
+  if (accel == RT_MESH_LBVH_GPU && nTri > 32) {
+    rt_scene *s = nullptr;
+    int rc = scene_begin(out, s);
+    if (rc) return rc;
+    DeviceBvh d;
+    std::string derr;
+    if (!build_bvh8_device(vpos4, n_verts, indices, n_indices, d, derr)) {
+      scene_free(s);
+      return fail(derr.find("index out of range") != std::string::npos || derr.find("mesh needs") != std::string::npos
+                      ? RT_ERR_INVALID
+                      : RT_ERR_CUDA,
+                  derr);
+    }
+    s->allocs.push_back(d.nodes);
+    s->allocs.push_back(d.tris);
+    s->bytes += (uint64_t)d.n_nodes * sizeof(BvhNode) + (uint64_t)d.n_tris * sizeof(TriDev);
+    s->kind = RT_SCENE_MESH;
+    s->dev.kind = RT_SCENE_MESH;
+    MeshDev &m = s->dev.mesh;
+    m.nodes = d.nodes;
+    m.tris = d.tris;
+    m.n_nodes = d.n_nodes;
+    m.n_tris = d.n_tris;
+    m.brute = 0u;
+    m.literal_order = 0u;
+    s->build_ms = d.build_ms;
+    for (int a = 0; a < 3; ++a) {
+      s->bbox_min[a] = d.bbox_min[a];
+      s->bbox_max[a] = d.bbox_max[a];
+    }
+    rc = scene_finish(s, out);
+    if (rc != RT_OK) scene_free(s);
+    return rc;
+  }
+  if (accel == RT_MESH_LBVH_GPU) accel = RT_MESH_AUTO;  // tiny meshes: nothing to build
   // brute force keeps the whole mesh in shared memory: 48 B per triangle, up to 4096 triangles (192 KB)
   if (accel == RT_MESH_AUTO) accel = nTri <= 32 ? RT_MESH_BRUTE : RT_MESH_BVH8;
   if (accel == RT_MESH_BRUTE && nTri > 4096) return fail(RT_ERR_UNSUPPORTED, "brute force is limited to 4096 triangles");
@@ -314,6 +350,14 @@ int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32
 }
 
 void rt_scene_destroy(rt_scene *scene) { scene_free(scene); }
+
+int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tris, float *device_build_ms) {
+  if (!scene || scene->kind != RT_SCENE_MESH) return fail(RT_ERR_INVALID, "not a mesh scene");
+  if (n_nodes) *n_nodes = scene->dev.mesh.n_nodes;
+  if (n_tris) *n_tris = scene->dev.mesh.n_tris;
+  if (device_build_ms) *device_build_ms = scene->build_ms;
+  return RT_OK;
+}
 
 int rt_scene_kind_of(const rt_scene *scene) { return scene ? scene->kind : RT_ERR_INVALID; }
 int rt_scene_device(const rt_scene *scene) { return scene ? scene->device : RT_ERR_INVALID; }

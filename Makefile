@@ -12,7 +12,7 @@ EXAMPLE := $(HOST)/example_frame_loop
 
 all: $(OUT) $(EXAMPLE)
 
-$(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o $(OBJ)/bvh_gpu.o $(OBJ)/rt_host.o
+$(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o $(OBJ)/bvh_gpu.o $(OBJ)/ingest.o $(OBJ)/rt_host.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart shared
 
 # host mirror of the reference's C++ interface (pure host code; -ffp-contract=off keeps the camera matrices
@@ -32,11 +32,15 @@ $(OBJ)/rt_kernels_fast.o: $(CSRC)/rt_kernels_fast.cu $(CSRC)/rt_kernels.cuh $(CS
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -fmad=true -c $< -o $@
 
-$(OBJ)/rt_api.o: $(CSRC)/rt_api.cu $(CSRC)/rt_scene.h $(CSRC)/bvh_builder.h include/rt_b200.h
+$(OBJ)/rt_api.o: $(CSRC)/rt_api.cu $(CSRC)/rt_scene.h $(CSRC)/bvh_builder.h $(CSRC)/ingest.h include/rt_b200.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
 $(OBJ)/bvh_gpu.o: $(CSRC)/bvh_gpu.cu $(CSRC)/bvh_builder.h $(CSRC)/rt_scene.h include/rt_b200.h
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(OBJ)/ingest.o: $(CSRC)/ingest.cu $(CSRC)/ingest.h $(CSRC)/rt_scene.h include/rt_b200.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 

@@ -237,7 +237,7 @@ def run_cuda(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     rt.set_math_mode(rt.MATH_FAST if args.math == "fast" else rt.MATH_EXACT)
-    rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT}[args.sched])
+    rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT, "compact": rt.SCHED_COMPACT}[args.sched])
 
     g, scene_name, c, W, H = load_workload(args.scene)
     t_build = time.perf_counter()
@@ -522,7 +522,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=("cuda", "reference"))
     ap.add_argument("--scene", default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument("--math", default="exact", choices=("exact", "fast"))
-    ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent"))
+    ap.add_argument("--sched", default="auto", choices=("auto", "tiles", "persistent", "compact"))
     ap.add_argument("--mesh-accel", default="auto", choices=("auto", "host", "lbvh_gpu"),
                     help="who builds the 8-wide BVH: the host (binned SAH) or the device (linear BVH)")
     ap.add_argument("--band-rows", type=int, default=8,

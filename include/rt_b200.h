@@ -47,10 +47,19 @@ typedef enum rt_math_mode { RT_MATH_EXACT = 0, RT_MATH_FAST = 1 } rt_math_mode;
 
 /* Ray-to-thread scheduling of the render kernels.
  * RT_SCHED_TILES     : one thread per pixel, 8x4-pixel warp tiles, one launch covers the frame.
- * RT_SCHED_PERSISTENT: persistent warps pull 8x4 tiles from an atomic counter and refill retired lanes
- *   (ballot compaction) so early-terminating rays do not idle a warp.
+ * RT_SCHED_PERSISTENT: persistent warps pull 8x4 tiles from an atomic counter, so warps whose rays all end
+ *   early pick up new work at once.
+ * RT_SCHED_COMPACT   : persistent warps as a pool of 32 ray slots: finished lanes are refilled from the pixel
+ *   counter (ballot + popc, one warp-aggregated atomic) and lanes standing on a leaf march in batches.  Octree
+ *   scenes without plane / secondary rays; anything else runs as RT_SCHED_PERSISTENT.  Bit-identical output;
+ *   measured slower than PERSISTENT on B200, kept selectable.
  * RT_SCHED_AUTO      : the per-scene-type default chosen by measurement. */
-typedef enum rt_sched_mode { RT_SCHED_AUTO = 0, RT_SCHED_TILES = 1, RT_SCHED_PERSISTENT = 2 } rt_sched_mode;
+typedef enum rt_sched_mode {
+  RT_SCHED_AUTO = 0,
+  RT_SCHED_TILES = 1,
+  RT_SCHED_PERSISTENT = 2,
+  RT_SCHED_COMPACT = 3
+} rt_sched_mode;
 
 /* Dense-grid storage in HBM. LINEAR = the on-disk order (x-major, z fastest, grid_raytracing.hpp:13-15);
  * BRICKS = 8x8x8-sample bricks so the 8 corners of a trilinear cell share few 128-byte lines. */
@@ -131,6 +140,8 @@ int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32
 /* mesh scenes: size of the tree and, for RT_MESH_LBVH_GPU, the device time of its construction (0 otherwise).
  * Any output pointer may be NULL. */
 int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tris, float *device_build_ms);
+/* device time (ms) of the on-device part of scene construction: octree split + validation, RT_MESH_LBVH_GPU build */
+int rt_scene_build_ms(const rt_scene *scene, float *device_ms);
 void rt_scene_destroy(rt_scene *scene);
 int rt_scene_kind_of(const rt_scene *scene);             /* rt_scene_kind */
 int rt_scene_device(const rt_scene *scene);

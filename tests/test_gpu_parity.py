@@ -55,7 +55,7 @@ def _frame(c, **kw):
     return rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"], **kw)
 
 
-@pytest.mark.parametrize("sched", (rt.SCHED_TILES, rt.SCHED_PERSISTENT))
+@pytest.mark.parametrize("sched", (rt.SCHED_TILES, rt.SCHED_PERSISTENT, rt.SCHED_COMPACT))
 @pytest.mark.parametrize("key", SDF_CASES)
 def test_sdf_scenes_bit_exact_vs_reference(key, sched):
     rt.set_sched_mode(sched)

@@ -94,7 +94,7 @@ def test_large_sdf_standins_bit_exact_at_full_size(name, W, H):
     layouts = (rt.GRID_LINEAR, rt.GRID_BRICKS) if name.startswith("example_grid") else (None,)
     for layout in layouts:
         s = util.cuda_scene(G, name, **({"layout": layout} if layout is not None else {}))
-        for sched in (rt.SCHED_TILES, rt.SCHED_PERSISTENT):
+        for sched in (rt.SCHED_TILES, rt.SCHED_PERSISTENT, rt.SCHED_COMPACT):
             rt.set_sched_mode(sched)
             r = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), want_prim=True, want_counters=True)
             assert util.same_bits(r["t"], want_t) and np.array_equal(r["color"], want_c), (name, layout, sched)

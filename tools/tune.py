@@ -12,7 +12,7 @@ def point(scene_name, sched):
     from triangles_sdf_cpu_raytracing_b200 import _lib as L
     import bench
     g, sname, c, W, H = bench.load_workload(scene_name)
-    rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT}[sched])
+    rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT, "compact": rt.SCHED_COMPACT}[sched])
     from tests import util
     scene = util.cuda_scene(g, sname)
     frame = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True)

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "librt_b200.so")
 RT_OK = 0
 SHADE_NORMAL, SHADE_LAMBERT, SHADE_COLOR = 0, 1, 2
 MATH_EXACT, MATH_FAST = 0, 1
-SCHED_AUTO, SCHED_TILES, SCHED_PERSISTENT = 0, 1, 2
+SCHED_AUTO, SCHED_TILES, SCHED_PERSISTENT, SCHED_COMPACT = 0, 1, 2, 3
 GRID_AUTO, GRID_LINEAR, GRID_BRICKS = 0, 1, 2
 MESH_AUTO, MESH_BVH8, MESH_BRUTE, MESH_LBVH_GPU = 0, 1, 2, 3
 SCENE_GRID, SCENE_OCTREE, SCENE_MESH = 0, 1, 2
@@ -50,6 +50,7 @@ SIGNATURES = {
     "rt_scene_create_octree": (_i, [_vp, _u32, _pp]),
     "rt_scene_create_mesh": (_i, [_vp, _u32, _vp, _u32, _i, _pp]),
     "rt_scene_create_mesh_bvh8": (_i, [_vp, _u32, _vp, _u32, _vp, _u32, _u32, _vp, _pp]),
+    "rt_scene_build_ms": (_i, [_vp, C.POINTER(_f)]),
     "rt_scene_mesh_stats": (_i, [_vp, C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_f)]),
     "rt_scene_destroy": (None, [_vp]),
     "rt_scene_kind_of": (_i, [_vp]),

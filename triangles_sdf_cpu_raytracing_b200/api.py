@@ -67,6 +67,12 @@ class Scene:
         L.check(L.lib().rt_scene_info(self._h, C.byref(b), lo, hi))
         return dict(device_bytes=int(b.value), bbox_min=np.array(lo[:], np.float32), bbox_max=np.array(hi[:], np.float32))
 
+    def build_ms(self) -> float:
+        """Device time of the on-device part of scene construction (octree ingestion, device BVH build)."""
+        ms = C.c_float()
+        L.check(L.lib().rt_scene_build_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
     def mesh_stats(self):
         """Mesh scenes: dict(n_nodes, n_tris, device_build_ms) (device_build_ms is 0 for host-built trees)."""
         n, t, ms = C.c_uint32(), C.c_uint32(), C.c_float()

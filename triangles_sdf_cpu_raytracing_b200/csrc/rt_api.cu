@@ -13,6 +13,7 @@
 #include <cuda_runtime.h>
 
 #include "bvh_builder.h"
+#include "ingest.h"
 #include "rt_scene.h"
 
 using namespace rt;
@@ -164,7 +165,7 @@ int rt_set_math_mode(int mode) {
 }
 
 int rt_set_sched_mode(int mode) {
-  if (mode < RT_SCHED_AUTO || mode > RT_SCHED_PERSISTENT) return fail(RT_ERR_INVALID, "unknown sched mode");
+  if (mode < RT_SCHED_AUTO || mode > RT_SCHED_COMPACT) return fail(RT_ERR_INVALID, "unknown sched mode");
   g_sched = mode;
   return RT_OK;
 }
@@ -189,18 +190,20 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   const size_t n = (size_t)sx * sy * sz;
   if (layout == RT_GRID_AUTO) layout = RT_GRID_LINEAR;  // chosen by measurement, DESIGN.md "grid layout"
   if (layout == RT_GRID_BRICKS) {
-    const uint32_t nbx = (sx + 7) / 8, nby = (sy + 7) / 8, nbz = (sz + 7) / 8;
-    std::vector<float> b((size_t)nbx * nby * nbz * 512, 0.0f);
-    for (uint32_t x = 0; x < sx; ++x)
-      for (uint32_t y = 0; y < sy; ++y) {
-        const float *src = values + ((size_t)x * sy + y) * sz;
-        for (uint32_t z = 0; z < sz; ++z) {
-          size_t br = ((size_t)(x >> 3) * nby + (y >> 3)) * nbz + (z >> 3);
-          b[(br << 9) + (((x & 7u) << 6) | ((y & 7u) << 3) | (z & 7u))] = src[z];
-        }
-      }
+    // the layout transform runs on the device (ingest.cu): upload the linear samples once, re-tile there
+    const uint32_t nby = (sy + 7) / 8, nbz = (sz + 7) / 8;
+    float *b = nullptr;
+    size_t count = 0;
+    std::string ierr;
+    const int irc = ingest_grid_bricks_device(values, sx, sy, sz, &b, &count, ierr);
+    if (irc != INGEST_OK) {
+      scene_free(s);
+      return fail(RT_ERR_CUDA, ierr);
+    }
+    s->allocs.push_back(b);
+    s->bytes += count * sizeof(float);
+    g.values = b;
     g.bricks = 1; g.stride_x = nby * nbz * 512u; g.stride_y = nbz * 512u;
-    rc = upload(s, b.data(), b.size(), &g.values);
   } else {
     g.bricks = 0; g.stride_x = sy * sz; g.stride_y = sz;
     rc = upload(s, values, n, &g.values);
@@ -213,56 +216,29 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
 // -------------------------------------------------------------------------------------------- octree
 int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out) {
   if (!nodes36 || n_nodes == 0) return fail(RT_ERR_INVALID, "octree needs at least the root node");
-  const uint8_t *raw = static_cast<const uint8_t *>(nodes36);
-  std::vector<uint32_t> link(n_nodes);
-  std::vector<float> vals((size_t)n_nodes * 8);
-  for (uint32_t i = 0; i < n_nodes; ++i) {
-    std::memcpy(&vals[(size_t)i * 8], raw + (size_t)i * 36, 32);
-    std::memcpy(&link[i], raw + (size_t)i * 36 + 32, 4);
-  }
-  // validate: every inner node's 8 children in range, each node reached at most once (a tree), bounded depth
-  std::vector<uint8_t> seen(n_nodes, 0);
-  std::vector<std::pair<uint32_t, uint32_t>> stack{{0u, 0u}};
-  seen[0] = 1;
-  uint32_t depth = 0;
-  while (!stack.empty()) {
-    auto [node, lvl] = stack.back();
-    stack.pop_back();
-    depth = std::max(depth, lvl);
-    uint32_t off = link[node];
-    if (off == 0) continue;
-    if ((uint64_t)off + 7 >= n_nodes) return fail(RT_ERR_INVALID, "octree childrenOffset out of range");
-    if (lvl + 1 > (uint32_t)OCT_MAX_DEPTH) return fail(RT_ERR_INVALID, "octree deeper than the supported 21 levels");
-    for (uint32_t c = 0; c < 8; ++c) {
-      if (seen[off + c]) return fail(RT_ERR_INVALID, "octree node referenced twice (not a tree)");
-      seen[off + c] = 1;
-      stack.push_back({off + c, lvl + 1});
-    }
-  }
-  // leaf classification, from the values alone: isEmpty (octree_raytracing.hpp:12-17) or all >= 1e-4 (.cpp:132-135)
-  for (uint32_t i = 0; i < n_nodes; ++i) {
-    if (link[i] != 0) continue;
-    const float *v = &vals[(size_t)i * 8];
-    bool allBig = true, allZero = true, allPos = true;
-    for (int k = 0; k < 8; ++k) {
-      if (!(v[k] > 10.0f)) allBig = false;
-      if (!(v[k] == 0.0f)) allZero = false;
-      if (!(v[k] >= 1e-4f)) allPos = false;
-    }
-    link[i] = (allBig || allZero || allPos) ? OCT_LEAF_CULLED : OCT_LEAF_SURFACE;
-  }
+  // Split, leaf classification and validation run on the device (ingest.cu): the raw records are uploaded as they are.
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
   if (rc) return rc;
+  uint32_t *link = nullptr, depth = 0;
+  float4 *vals = nullptr;
+  std::string ierr;
+  const int irc = ingest_octree_device(nodes36, n_nodes, &link, &vals, &depth, &s->build_ms, ierr);
+  if (irc != INGEST_OK) {
+    scene_free(s);
+    return fail(irc == INGEST_INVALID ? RT_ERR_INVALID : RT_ERR_CUDA, ierr);
+  }
+  s->allocs.push_back(link);
+  s->allocs.push_back(vals);
+  s->bytes += (uint64_t)n_nodes * 36;
   s->kind = RT_SCENE_OCTREE;
   s->dev.kind = RT_SCENE_OCTREE;
   s->dev.oct.n_nodes = n_nodes;
   s->dev.oct.depth = depth;
-  rc = upload(s, link.data(), link.size(), &s->dev.oct.link);
-  const float *dv = nullptr;
-  if (rc == RT_OK) rc = upload(s, vals.data(), vals.size(), &dv);
-  s->dev.oct.values = reinterpret_cast<const float4 *>(dv);
-  if (rc == RT_OK) rc = scene_finish(s, out);
+  s->dev.oct.root_inner = depth > 0 ? 1u : 0u;
+  s->dev.oct.link = link;
+  s->dev.oct.values = vals;
+  rc = scene_finish(s, out);
   if (rc != RT_OK) scene_free(s);
   return rc;
 }
@@ -351,6 +327,12 @@ int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32
 
 void rt_scene_destroy(rt_scene *scene) { scene_free(scene); }
 
+int rt_scene_build_ms(const rt_scene *scene, float *device_ms) {
+  if (!scene || !device_ms) return fail(RT_ERR_INVALID, "null argument");
+  *device_ms = scene->build_ms;
+  return RT_OK;
+}
+
 int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tris, float *device_build_ms) {
   if (!scene || scene->kind != RT_SCENE_MESH) return fail(RT_ERR_INVALID, "not a mesh scene");
   if (n_nodes) *n_nodes = scene->dev.mesh.n_nodes;
@@ -426,6 +408,8 @@ int env_int(const char *name) {
 }
 const int g_env_tile_block = env_int("RT_TILE_BLOCK");
 const int g_env_host_chunks = env_int("RT_HOST_CHUNKS");
+const int g_env_oct_refill = env_int("RT_OCT_REFILL");
+const int g_env_oct_batch = env_int("RT_OCT_BATCH");
 
 // per-scene-type default scheduling, chosen by measurement (profiles/r1_tune.txt): the octree
 // descent has the most uneven per-warp cost and gains from persistent warps pulling tiles; the grid marcher, the BVH
@@ -450,6 +434,9 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   rt_scene *ms = const_cast<rt_scene *>(scene);
   a.tile_counter = scene->tile_counters + (ms->next_counter.fetch_add(1) % N_TILE_COUNTERS);
   a.tile_block = g_env_tile_block;
+  // RT_SCHED_COMPACT thresholds: best point of the sweep in profiles/r1_tune.txt (RT_OCT_REFILL / RT_OCT_BATCH override)
+  a.oct_refill_min = g_env_oct_refill > 0 ? g_env_oct_refill : 32;
+  a.oct_leaf_batch = g_env_oct_batch > 0 ? g_env_oct_batch : 6;
   const int sched = resolve_sched(scene);
   cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, scene->sm_count, st)
                                                   : exact::launch_render(a, sched, scene->sm_count, st);

@@ -535,6 +535,113 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   return r;
 }
 
+// ---- the same descent as a resumable per-lane state machine (render_octree_compact_kernel) ------------------------
+// oct_intersect above runs one ray to completion; here the loop body is exposed one child visit at a time so that a
+// persistent warp can (a) hand a lane a NEW ray the moment its old one is done and (b) hold lanes that stand on a
+// surface leaf until enough of them can march together.  Same functions, same operands, same order per ray.
+struct OctWalk {
+  V3 d, inv;
+  float tFar;
+  uint32_t flags;  // bit 0 finiteInv, bit 1 fastOk, bits 4..6 nearMask
+  int level;
+  V3 bmin;
+  float ext, invExt;
+  unsigned long long path;
+  uint32_t closedMask, cbase, w;
+  uint32_t pend[OCT_MAX_DEPTH + 1], base[OCT_MAX_DEPTH + 1];
+  // pending surface leaf
+  uint32_t leafNode;
+  V3 leafMin;
+  float leafExt, leafInvExt;
+  bool leafClosed;
+};
+constexpr int OCT_WALK_CONTINUE = 0, OCT_WALK_LEAF = 1, OCT_WALK_DONE = 2;
+
+// the root must be an inner node (the caller checks OctreeDev::root_inner)
+template <bool COUNT>
+__device__ __forceinline__ void oct_walk_begin(OctWalk &s, const OctreeDev &oc, V3 o, V3 d, float tNear, float tFar,
+                                               Counters &cnt) {
+  s.d = d;
+  s.inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  s.tFar = tFar;
+  const bool finiteInv = isfinite(s.inv.x) && isfinite(s.inv.y) && isfinite(s.inv.z);
+  const bool fastOk = finiteInv && s.inv.x != 0.0f && s.inv.y != 0.0f && s.inv.z != 0.0f && tNear > 0.0f && tFar >= tNear;
+  const uint32_t nearMask = (s.inv.x < 0.0f ? 4u : 0u) | (s.inv.y < 0.0f ? 2u : 0u) | (s.inv.z < 0.0f ? 1u : 0u);
+  s.flags = (finiteInv ? 1u : 0u) | (fastOk ? 2u : 0u) | (nearMask << 4);
+  s.level = 0;
+  s.bmin = mk3(-1.0f, -1.0f, -1.0f);
+  s.ext = 2.0f;
+  s.invExt = 0.5f;
+  s.path = 0;
+  s.cbase = __ldg(oc.link);
+  if (COUNT) cnt.oct_inner++;
+  bool cf;
+  s.w = oct_children(s.bmin, s.ext, o, s.inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+  s.closedMask = cf ? 1u : 0u;
+}
+
+// one iteration of oct_intersect's loop, without the leaf march
+template <bool COUNT>
+__device__ __forceinline__ int oct_walk_step(OctWalk &s, const OctreeDev &oc, V3 o, float tNear, Counters &cnt) {
+  if (s.w == 0) {
+    if (s.level == 0) return OCT_WALK_DONE;
+    --s.level;
+    s.w = s.pend[s.level];
+    s.cbase = s.base[s.level];
+    const uint32_t id = (uint32_t)s.path & 7u;
+    s.path >>= 3;
+    s.bmin = mk3(s.bmin.x - ((id & 4u) ? s.ext : 0.0f), s.bmin.y - ((id & 2u) ? s.ext : 0.0f),
+                 s.bmin.z - ((id & 1u) ? s.ext : 0.0f));
+    s.ext *= 2.0f;
+    s.invExt *= 0.5f;
+    return OCT_WALK_CONTINUE;
+  }
+  const uint32_t id = s.w & 7u;
+  s.w >>= 4;
+  const uint32_t child = s.cbase + id;
+  const uint32_t link = __ldg(oc.link + child);
+  const float h = s.ext * 0.5f;
+  const V3 cmin = mk3(s.bmin.x + ((id & 4u) ? h : 0.0f), s.bmin.y + ((id & 2u) ? h : 0.0f), s.bmin.z + ((id & 1u) ? h : 0.0f));
+  if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
+    if (COUNT) cnt.oct_leaf++;
+    if (link == OCT_LEAF_CULLED) return OCT_WALK_CONTINUE;
+    s.leafNode = child;
+    s.leafMin = cmin;
+    s.leafExt = h;
+    s.leafInvExt = s.invExt * 2.0f;
+    s.leafClosed = ((s.closedMask >> s.level) & 1u) != 0u;
+    return OCT_WALK_LEAF;
+  }
+  if (COUNT) cnt.oct_inner++;
+  s.pend[s.level] = s.w;
+  s.base[s.level] = s.cbase;
+  ++s.level;
+  s.path = (s.path << 3) | id;
+  s.bmin = cmin;
+  s.ext = h;
+  s.invExt *= 2.0f;
+  s.cbase = link;
+  bool cf;
+  s.w = oct_children(s.bmin, s.ext, o, s.inv, (s.flags & 1u) != 0u, (s.flags & 2u) != 0u, (s.flags >> 4) & 7u, tNear,
+                     s.tFar, cf);
+  s.closedMask = (s.closedMask & ~(1u << s.level)) | (cf ? (1u << s.level) : 0u);
+  return OCT_WALK_CONTINUE;
+}
+
+// march the pending leaf; on a hit fills r (t, prim, normal) exactly as oct_intersect does
+template <bool COUNT>
+__device__ __forceinline__ bool oct_walk_leaf(const OctWalk &s, const OctreeDev &oc, V3 o, float tNear, Hit &r,
+                                              Counters &cnt) {
+  V3 pHit;
+  if (!oct_leaf<COUNT>(oc, s.leafNode, s.leafMin, s.leafExt, s.leafInvExt, o, s.d, s.inv, tNear, s.tFar, s.leafClosed, r,
+                       pHit, cnt))
+    return false;
+  const float4 a = __ldg(oc.values + 2 * (size_t)r.prim), b = __ldg(oc.values + 2 * (size_t)r.prim + 1);
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  r.normal = oct_node_normal(v, s.leafMin, s.leafInvExt, pHit);
+  return true;
+}
+
 // =============================================================================================================
 // Triangle mesh: 8-wide BVH (triangles_raytracing.cpp:266-335) and brute force (ray_pack.ispc:167-202)
 // =============================================================================================================

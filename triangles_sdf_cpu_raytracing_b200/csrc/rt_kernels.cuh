@@ -289,6 +289,121 @@ __global__ void __launch_bounds__(BLOCK_THREADS) render_persistent_kernel(const 
   if (COUNT) flush_counters(cnt, a.counters);
 }
 
+// ---- octree, persistent warps with lane refill and batched leaf marches ------------------------------------------
+// The north-star scheduling (RT_SCHED_COMPACT) for the most divergent scene type.  MEASURED AND NOT THE DEFAULT: the
+// resumable state (OctWalk in local memory, three votes per iteration) costs more than the idle lanes it recovers:
+// octree6 4K 0.73 ms persistent tiles vs 1.00 ms here at the best thresholds, depth-8 stand-in 1.16 vs 1.59 ms
+// (profiles/r1_tune.txt).  Kept selectable and parity-tested.  A warp is a pool of 32 independent ray slots:
+//   * a lane whose ray is finished goes IDLE; when enough lanes are idle (or nothing else is left to do) the idle lanes
+//     take the next pixels from a global counter with ONE warp-aggregated atomicAdd (ballot + popc give each lane its
+//     rank) and generate their rays together;
+//   * lanes that stand on a surface leaf wait (state LEAF) until OCT_LEAF_BATCH of them can march together, or no
+//     lane is left walking: the leaf march used to run at 5..13 of 32 lanes (profiles/r1_octree*_lines.txt);
+//   * every iteration the warp votes (ballot) for one phase: refill, walk one child, or march.
+// Per-ray arithmetic is oct_intersect's, so the frame is bit-identical; primary rays only (no plane / secondary rays).
+constexpr int OCT_IDLE = 0, OCT_TRAV = 1, OCT_LEAF = 2;
+
+// primary-ray part of Renderer::intersectionColor (raytracing.cpp:23-50) for a hit without secondary rays
+__device__ __forceinline__ C4 shade_primary(const FrameDev &f, V3 o, V3 d, Hit &hit) {
+  if (dot3(hit.normal, d) > 0) hit.normal = scale3(hit.normal, -1.0f);
+  C4 color;
+  if (f.mode == RT_SHADE_NORMAL) {
+    color.r = (hit.normal.x + 1.0f) / 2.0f;
+    color.g = (hit.normal.y + 1.0f) / 2.0f;
+    color.b = (hit.normal.z + 1.0f) / 2.0f;
+    color.a = (1.0f + 1.0f) / 2.0f;
+  } else if (f.mode == RT_SHADE_COLOR) {
+    color.r = color.g = color.b = hit.albedo;
+    color.a = 1.0f;
+  } else {
+    color = lambert_color(hit, along(o, d, hit.t), mk3(f.light[0], f.light[1], f.light[2]), true);
+  }
+  return color;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128) render_octree_compact_kernel(const __grid_constant__ RenderArgs a) {
+  const FrameDev &f = a.frame;
+  const OctreeDev &oc = a.scene.oct;
+  const uint32_t lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+  const uint32_t tilesX = (f.W + TILE_W - 1) / TILE_W, tilesY = (f.rows_here + TILE_H - 1) / TILE_H;
+  const uint32_t nSlots = tilesX * tilesY * 32u;  // pixel slots in tile order (some fall outside the frame)
+  const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
+  const float INF = __int_as_float(0x7f800000);
+  Counters cnt = {};
+  OctWalk s;
+  int state = OCT_IDLE;
+  size_t px = 0;
+  bool exhausted = false;
+  for (;;) {
+    const uint32_t idle = __ballot_sync(0xffffffffu, state == OCT_IDLE);
+    // ---- refill: idle lanes take the next pixel slots
+    if (!exhausted && idle != 0u && (__popc(idle) >= a.oct_refill_min || idle == 0xffffffffu)) {
+      const uint32_t n = (uint32_t)__popc(idle), leader = (uint32_t)__ffs(idle) - 1u;
+      uint32_t first = 0;
+      if (lane == leader) first = atomicAdd(a.tile_counter, n);
+      first = __shfl_sync(0xffffffffu, first, leader);
+      if (first + n >= nSlots) exhausted = true;
+      if (state == OCT_IDLE) {
+        const uint32_t slot = first + (uint32_t)__popc(idle & ltMask);
+        if (slot < nSlots) {
+          const uint32_t tile = slot >> 5, in = slot & 31u;
+          const uint32_t tyi = tile / tilesX, tx = tile - tyi * tilesX, ty = centre_out(tyi, tilesY);
+          const uint32_t x = tx * TILE_W + (in & 7u), v = ty * TILE_H + (in >> 3);
+          const uint32_t row = (x < f.W && v < f.rows_here) ? band_row(f, v) : f.H;
+          if (row < f.H) {
+            px = (size_t)row * f.W + x;
+            const V3 d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
+            const float tPrev = (a.t_in && !f.clear) ? a.t_in[px] : INF;
+            if (COUNT) cnt.rays++;
+            oct_walk_begin<COUNT>(s, oc, o, d, f.t_near, std_min(f.t_far, tPrev), cnt);
+            state = OCT_TRAV;
+          }
+        }
+      }
+      continue;
+    }
+    const uint32_t trav = __ballot_sync(0xffffffffu, state == OCT_TRAV);
+    const uint32_t leaf = __ballot_sync(0xffffffffu, state == OCT_LEAF);
+    if ((trav | leaf) == 0u) {
+      if (exhausted) break;
+      continue;  // everyone idle: the refill branch fires next iteration
+    }
+    if (leaf != 0u && (__popc(leaf) >= a.oct_leaf_batch || trav == 0u)) {
+      // ---- march phase
+      if (state == OCT_LEAF) {
+        Hit hit = hit_none();
+        if (oct_walk_leaf<COUNT>(s, oc, o, f.t_near, hit, cnt)) {
+          if (COUNT) cnt.hits++;
+          const C4 col = shade_primary(f, o, s.d, hit);
+          a.t_out[px] = hit.t;
+          a.color[px] = color_pack_rgba(col);
+          if (a.prim) a.prim[px] = hit.prim;
+          state = OCT_IDLE;  // the first leaf that reports a hit ends the descent (octree_raytracing.cpp:188-197)
+        } else {
+          state = OCT_TRAV;
+        }
+      }
+    } else {
+      // ---- walk phase: one child visit per walking lane
+      if (state == OCT_TRAV) {
+        const int r = oct_walk_step<COUNT>(s, oc, o, f.t_near, cnt);
+        if (r == OCT_WALK_LEAF) {
+          state = OCT_LEAF;
+        } else if (r == OCT_WALK_DONE) {
+          if (f.clear) {  // fused FrameBuffer::clear (raytracing.hpp:16-19)
+            a.t_out[px] = INF;
+            a.color[px] = 0u;
+            if (a.prim) a.prim[px] = RT_PRIM_MISS;
+          }
+          state = OCT_IDLE;
+        }
+      }
+    }
+  }
+  if (COUNT) flush_counters(cnt, a.counters);
+}
+
 // ---- IScene::intersect for n arbitrary rays ---------------------------------------------------------------------
 template <int KIND>
 __global__ void __launch_bounds__(BLOCK_THREADS) rays_kernel(const __grid_constant__ RayArgs a) {
@@ -329,7 +444,18 @@ static cudaError_t launch_tiles_shape(const RenderArgs &a, size_t smem, cudaStre
 template <int KIND, bool COUNT, bool SECONDARY>
 static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count, cudaStream_t st) {
   const size_t smem = (KIND == KIND_BRUTE) ? (size_t)a.scene.mesh.n_tris * sizeof(TriDev) : 0;
-  if (sched == RT_SCHED_PERSISTENT) {
+  if (KIND == KIND_OCTREE && !SECONDARY && sched == RT_SCHED_COMPACT && a.scene.oct.root_inner && !a.frame.has_plane) {
+    auto kern = render_octree_compact_kernel<COUNT>;
+    int perSm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 128, 0);
+    if (e != cudaSuccess) return e;
+    if (perSm < 1) perSm = 1;
+    e = cudaMemsetAsync(a.tile_counter, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
+    kern<<<dim3((unsigned)(sm_count * perSm)), 128, 0, st>>>(a);
+    return cudaGetLastError();
+  }
+  if (sched == RT_SCHED_PERSISTENT || sched == RT_SCHED_COMPACT) {
     auto kern = render_persistent_kernel<KIND, COUNT, SECONDARY>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int perSm = 0;

@@ -35,6 +35,7 @@ struct OctreeDev {
   const float4 *values;
   uint32_t n_nodes;
   uint32_t depth;
+  uint32_t root_inner;  // 1: node 0 has children (always, except for a one-node file)
 };
 
 // ---- triangle mesh ------------------------------------------------------------------------------------
@@ -101,6 +102,7 @@ struct RenderArgs {
   unsigned long long *counters;  // rt_counters as 9 x u64, or null
   uint32_t *tile_counter;        // persistent scheduling: next tile to hand out
   int32_t tile_block;            // RT_SCHED_TILES: threads per block (32, 64, 128, 256)
+  int32_t oct_refill_min, oct_leaf_batch;  // RT_SCHED_COMPACT: idle lanes needed for a refill, leaf lanes for a march
 };
 
 struct RayArgs {

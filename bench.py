@@ -323,16 +323,17 @@ def run_cuda(args):
     barrier()
     step_no[0] = 0
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local) as clocks:
-        barrier()
-        for a, b in ev:
-            flush.zero_()  # evict the scene and the framebuffer from L2 between timed iterations (untimed)
-            if world > 1:
-                dist.barrier()
-            a.record()
-            step()
-            b.record()
-        barrier()
+    clocks = ClockSampler(local)
+    clocks.__enter__()  # sampled across all three device-timed loops below
+    barrier()
+    for a, b in ev:
+        flush.zero_()  # evict the scene and the framebuffer from L2 between timed iterations (untimed)
+        if world > 1:
+            dist.barrier()
+        a.record()
+        step()
+        b.record()
+    barrier()
     ms_total = sum(a.elapsed_time(b) for a, b in ev)
     if world > 1:
         tt = torch.tensor([ms_total], device=dev)
@@ -360,6 +361,7 @@ def run_cuda(args):
         b.record()
         kev.append((a, b))
     barrier()
+    clocks.__exit__()
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
 
     multi_frame = None
@@ -460,14 +462,21 @@ def run_cuda(args):
     fp32_peak = 148 * 128 * 2 * (clk["sm_mhz"] or sm_max) * 1e6 / 1e12  # TFLOP/s at the clock seen under load
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     scene_bytes = scene.info()["device_bytes"]
-    traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the committed ncu --set full captures
+    traffic, traffic_src, issue = None, None, None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")  # per launch, from the committed ncu --set full captures
     if os.path.exists(tp):
         ent = json.load(open(tp)).get(f"{args.scene}|{args.math}")
         if ent and world == 1:
             traffic, traffic_src = ent["dram_bytes_per_launch"], ent["source"]
+            # the operative bound of these kernels: warp instructions issued vs 1 per SM sub-partition per clock
+            peak_issue = 148 * 4 * peaks()[2] * 1e6 / 1e9
+            ach_issue = ent["warp_inst_per_launch"] / (kernel_ms * 1e-3) / 1e9
+            issue = {"warp_inst_per_launch": ent["warp_inst_per_launch"], "achieved_ginst_s": ach_issue,
+                     "peak_ginst_s": peak_issue, "frac": ach_issue / peak_issue, "lanes_active_of_32": ent["lanes_active"],
+                     "note": "148 SMs x 4 schedulers x 1 warp instruction per clock at the max SM clock; instruction "
+                             "count from the ncu capture, duration measured live"}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "traffic": traffic, "traffic_source": traffic_src, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
+                "traffic": traffic, "traffic_source": traffic_src, "issue": issue, "peak_source": f"{peak_kind} copy bandwidth (MEASURED_PEAKS.json)",
                 "kernel_ms": kernel_ms, "kernel_ms_warm_l2": kernel_ms_warm,
                 "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_flops_per_launch": alg_flops,
                 "rays_per_launch": rays_launch,

@@ -248,7 +248,9 @@ __device__ __forceinline__ uint32_t centre_out(uint32_t i, uint32_t n) {
 // so with long-tailed per-ray costs (one grazing ray marching 100+ steps) big blocks strand resident-warp slots
 // behind their slowest warp; the block shape per scene kind is chosen by measurement.
 template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY>
-__global__ void __launch_bounds__(32 * WX * WY) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
+// (BVH only: capping the traversal at 64 registers buys 8 resident blocks and measured 5 % on both meshes; the same cap
+// slows the grid and octree kernels, profiles/r1_tune.txt)
+__global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * WX * WY) : 0) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
   if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;

@@ -367,7 +367,12 @@ def run_cuda(args):
     multi_frame = None
     if world > 1:
         # the gathered frame of the last step, checked on rank 0 against the oracle below
+        # (orbit: render frame 0 once more, the camera the checker uses)
         barrier()
+        if orbit:
+            step_no[0] = 0
+            step()
+            barrier()
         if rank == 0:
             if shared is not None:
                 multi_frame = shared.download()

@@ -408,6 +408,7 @@ int env_int(const char *name) {
 }
 const int g_env_tile_block = env_int("RT_TILE_BLOCK");
 const int g_env_host_chunks = env_int("RT_HOST_CHUNKS");
+const int g_env_stage = std::getenv("RT_STAGE_STORES") ? env_int("RT_STAGE_STORES") : -1;  // -1: peer framebuffers only
 const int g_env_oct_refill = env_int("RT_OCT_REFILL");
 const int g_env_oct_batch = env_int("RT_OCT_BATCH");
 
@@ -434,6 +435,20 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   rt_scene *ms = const_cast<rt_scene *>(scene);
   a.tile_counter = scene->tile_counters + (ms->next_counter.fetch_add(1) % N_TILE_COUNTERS);
   a.tile_block = g_env_tile_block;
+  // Peer framebuffer (multi-GPU: rank 0's memory mapped over CUDA IPC): stage tiles in shared memory and store them as
+  // 128-byte TMA bulk writes.  Needs the fused clear (whole tiles are written) and 32-byte-multiple rows.
+  a.stage_stores = 0;
+  if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && g_env_stage != 0) {
+    bool peer = g_env_stage == 1;
+    if (!peer) {
+      cudaPointerAttributes pa;
+      if (cudaPointerGetAttributes(&pa, color) == cudaSuccess)
+        peer = pa.type == cudaMemoryTypeDevice && pa.device != scene->device;
+      else
+        cudaGetLastError();
+    }
+    a.stage_stores = peer ? 1 : 0;
+  }
   // RT_SCHED_COMPACT thresholds: best point of the sweep in profiles/r1_tune.txt (RT_OCT_REFILL / RT_OCT_BATCH override)
   a.oct_refill_min = g_env_oct_refill > 0 ? g_env_oct_refill : 32;
   a.oct_leaf_batch = g_env_oct_batch > 0 ? g_env_oct_batch : 6;

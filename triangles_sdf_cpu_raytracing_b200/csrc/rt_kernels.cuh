@@ -264,6 +264,60 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
   if (COUNT) flush_counters(cnt, a.counters);
 }
 
+// ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (multi-GPU: peer framebuffer) ----------
+// When the framebuffer lives on ANOTHER GPU (rank 0's, mapped over CUDA IPC) the plain kernel's stores cross NVLink as
+// 32-byte pieces (one 8-pixel tile row per warp).  Here a block owns 32 x 4 pixels: every thread parks its pixel in
+// shared memory, and after one barrier four threads issue the block's eight 128-byte row segments (colour + depth) as
+// bulk asynchronous stores (cp.async.bulk shared -> global, SASS UBLKCP): full 128-byte NVLink writes, no per-thread
+// store instructions.  Needs the fused clear (every pixel of the tile is written) and W % 8 == 0; primary rays only.
+template <int KIND>
+__global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
+  __shared__ __align__(128) uint32_t sColor[4][32];
+  __shared__ __align__(128) float sDepth[4][32];
+  const FrameDev &f = a.frame;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  const uint32_t x0 = blockIdx.x * 32u, v0 = centre_out(blockIdx.y, gridDim.y) * 4u;
+  const uint32_t lx = warp * TILE_W + (lane & 7u), ly = lane >> 3;
+  const uint32_t x = x0 + lx, v = v0 + ly;
+  Counters cnt = {};
+  if (x < f.W && v < f.rows_here) {
+    const uint32_t row = band_row(f, v);
+    if (row < f.H) {
+      const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
+      const V3 d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
+      C4 col;
+      float tNew = __int_as_float(0x7f800000);
+      uint32_t prim, packed = 0u;
+      if (intersection_color<KIND, false, false>(a.scene, f, nullptr, o, d, __int_as_float(0x7f800000), col, tNew, prim,
+                                                 cnt) &&
+          !isinf(tNew))
+        packed = color_pack_rgba(col);
+      else
+        tNew = __int_as_float(0x7f800000);
+      sColor[ly][lx] = packed;
+      sDepth[ly][lx] = tNew;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 4u) {
+    const uint32_t vr = v0 + threadIdx.x;
+    const uint32_t row = vr < f.rows_here ? band_row(f, vr) : f.H;
+    if (row < f.H && x0 < f.W) {
+      const uint32_t bytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
+      const size_t px = (size_t)row * f.W + x0;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> async proxy
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.color + px),
+                   "r"((uint32_t)__cvta_generic_to_shared(&sColor[threadIdx.x][0])), "r"(bytes)
+                   : "memory");
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.t_out + px),
+                   "r"((uint32_t)__cvta_generic_to_shared(&sDepth[threadIdx.x][0])), "r"(bytes)
+                   : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+  }
+}
+
 // ---- RT_SCHED_PERSISTENT: persistent warps, dynamic tile fetch ------------------------------------------------
 // Each warp repeatedly takes the next 8x4 tile from a global counter, so warps whose rays all terminate early
 // (box misses cost a few dozen instructions) immediately pick up new work instead of idling until the slowest
@@ -474,6 +528,11 @@ static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count,
     // a.tile_block (RT_TILE_BLOCK) overrides it for sweeps; only the plain primary-ray kernels have every shape.
     const int tb = a.tile_block;
     if (KIND == KIND_BRUTE) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
+    if (!COUNT && !SECONDARY && a.stage_stores) {
+      dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 3u) / 4u);
+      render_tiles_staged_kernel<KIND><<<grid, 128, 0, st>>>(a);
+      return cudaGetLastError();
+    }
     if (!COUNT && !SECONDARY) {
       if (tb == 32) return launch_tiles_shape<KIND, false, false, 1, 1>(a, smem, st);
       if (tb == 64) return launch_tiles_shape<KIND, false, false, 2, 1>(a, smem, st);

@@ -438,9 +438,10 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   // Peer framebuffer (multi-GPU: rank 0's memory mapped over CUDA IPC): stage tiles in shared memory and store them as
   // 128-byte TMA bulk writes.  Needs the fused clear (whole tiles are written) and 32-byte-multiple rows.
   a.stage_stores = 0;
+  int sched = resolve_sched(scene);
   if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && g_env_stage != 0) {
     bool peer = g_env_stage == 1;
-    if (!peer) {
+    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20)) {  // measured on 8 GPUs: pays at 4K, not at 1080p
       cudaPointerAttributes pa;
       if (cudaPointerGetAttributes(&pa, color) == cudaSuccess)
         peer = pa.type == cudaMemoryTypeDevice && pa.device != scene->device;
@@ -448,11 +449,13 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
         cudaGetLastError();
     }
     a.stage_stores = peer ? 1 : 0;
+    // the staged stores live in the tiles kernel: for a peer framebuffer the octree's default (persistent, ~1 % faster
+    // on one GPU) gives way to it
+    if (peer && g_sched.load() == RT_SCHED_AUTO) sched = RT_SCHED_TILES;
   }
   // RT_SCHED_COMPACT thresholds: best point of the sweep in profiles/r1_tune.txt (RT_OCT_REFILL / RT_OCT_BATCH override)
   a.oct_refill_min = g_env_oct_refill > 0 ? g_env_oct_refill : 32;
   a.oct_leaf_batch = g_env_oct_batch > 0 ? g_env_oct_batch : 6;
-  const int sched = resolve_sched(scene);
   cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, scene->sm_count, st)
                                                   : exact::launch_render(a, sched, scene->sm_count, st);
   if (e != cudaSuccess) return cuda_fail(e, "render launch");

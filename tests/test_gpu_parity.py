@@ -278,3 +278,34 @@ def test_fused_clear_equals_clear_then_draw():
         r = scene(c["scene"]).render(_frame(c, clear=True), color=dirty_c, t=dirty_t, want_prim=True)
         assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
         assert (r["prim"][~np.isfinite(c["t"])] == rt.PRIM_MISS).all()
+
+
+def test_staged_peer_store_kernel_is_bit_exact():
+    """The multi-GPU store path (tile parked in shared memory, 128-byte TMA bulk stores) forced on a local framebuffer:
+    RT_STAGE_STORES is read once at load, so the check runs in its own process."""
+    import os
+    import subprocess
+    import sys
+    code = """
+import numpy as np, torch
+import triangles_sdf_cpu_raytracing_b200 as rt
+from tests import util
+g = util.Golden()
+for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "stanford-bunny|default|160x90", "sdf_6|orbit23tilt|96x64"):
+    c = g.case(key)
+    s = util.cuda_scene(g, c["scene"])
+    W, H = c["W"], c["H"]
+    color = torch.full((H * W,), 0x5A5A5A5A, dtype=torch.int32, device="cuda")
+    t = torch.full((H * W,), 0.25, dtype=torch.float32, device="cuda")
+    for bands in (None, (8, 3, 1)):
+        f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True, bands=bands)
+        s.render_device(f, color.data_ptr(), None, t.data_ptr())
+    torch.cuda.synchronize()
+    assert util.same_bits(t.cpu().numpy().reshape(H, W), c["t"]), key
+    assert np.array_equal(color.cpu().numpy().view(np.uint32).reshape(H, W), c["color_normal"]), key
+print("staged ok")
+"""
+    env = dict(os.environ, RT_STAGE_STORES="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "staged ok" in r.stdout, r.stdout + r.stderr

@@ -21,7 +21,7 @@ import numpy as np
 
 from . import _lib as L
 
-DEFAULT_BAND_ROWS = 32
+DEFAULT_BAND_ROWS = 8  # = the block height of the tiles kernels; 135 bands at 1080p balance 8 ranks to 6 %
 
 
 def band_rows_of(height: int, band_rows: int, band_count: int, band_index: int) -> np.ndarray:

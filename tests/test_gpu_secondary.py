@@ -140,3 +140,23 @@ def test_cpp_frame_loop_obj_mesh(tmp_path):
     color, t = _run_example([str(tmp_path / "c.obj"), "128", "128", "normal", "0"], 128, 128, tmp_path / "o.raw")
     assert util.same_bits(t, want["t"]) and np.array_equal(color, want["color"])
     assert np.isfinite(t).mean() > 0.3
+
+
+def test_cpp_frame_loop_ppm_sink(tmp_path):
+    """SURVEY 8(f)-4, the step after the path: frames leave as binary PPM files (one per orbit frame) instead of an
+    SDL blit; the RGB bytes are the colour buffer's."""
+    exe = os.path.join(ROOT, "triangles_sdf_cpu_raytracing_b200", "hostapi", "example_frame_loop")
+    if not os.path.exists(exe):
+        pytest.skip("example_frame_loop has not been built (make)")
+    _write_grid(tmp_path / "g.grid", G.scene_arrays("example_grid")["values"])
+    p = subprocess.run([exe, str(tmp_path / "g.grid"), "96", "64", "normal", "0", str(tmp_path / "f.ppm"), "5"],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    names = sorted(n for n in os.listdir(tmp_path) if n.endswith(".ppm"))
+    assert names == [f"f_{k:03d}.ppm" for k in range(6)]
+    raw = open(tmp_path / "f_005.ppm", "rb").read()
+    head = b"P6\n96 64\n255\n"
+    assert raw.startswith(head) and len(raw) == len(head) + 96 * 64 * 3
+    rgb = np.frombuffer(raw[len(head):], np.uint8).reshape(64, 96, 3)
+    want = G.case("example_grid|orbit5|96x64")["color_normal"].view(np.uint8).reshape(64, 96, 4)[..., :3]
+    assert np.array_equal(rgb, want)

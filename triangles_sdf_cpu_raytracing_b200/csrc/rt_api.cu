@@ -187,6 +187,7 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   GridDev &g = s->dev.grid;
   g.sx = sx; g.sy = sy; g.sz = sz;
   g.fx = (float)(sx - 1); g.fy = (float)(sy - 1); g.fz = (float)(sz - 1);
+  g.hfx = 0.5f * g.fx; g.hfy = 0.5f * g.fy; g.hfz = 0.5f * g.fz;
   const size_t n = (size_t)sx * sy * sz;
   if (layout == RT_GRID_AUTO) layout = RT_GRID_LINEAR;  // chosen by measurement, DESIGN.md "grid layout"
   if (layout == RT_GRID_BRICKS) {

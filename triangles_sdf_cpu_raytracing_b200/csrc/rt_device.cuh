@@ -168,11 +168,14 @@ __device__ __forceinline__ uint32_t grid_offz(uint32_t z) {
 
 // SDFGrid::sdf(float3), grid_raytracing.cpp:7-62; cell = (c0x, c0y, c0z) packed by the caller when it wants the
 // grid's "prim id".  ceil(p) is evaluated as floor(p) + (p != floor(p)), the same value for 0 <= p < 2^23.
+// (A real branch for the c1 == c0 case instead of the selects below was measured and rejected: the case is not rare,
+// every ray's first sample sits exactly on the box face it entered through; grid 4K 0.338 -> 0.373 ms.)
 template <bool BRICKS, bool COUNT>
 __device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell, Counters &cnt) {
   if (COUNT) cnt.grid_samples++;
-  p.x = (p.x + 1.0f) / 2.0f; p.y = (p.y + 1.0f) / 2.0f; p.z = (p.z + 1.0f) / 2.0f;
-  p.x *= g.fx; p.y *= g.fy; p.z *= g.fz;  // (float)(size - 1)
+  // ((p + 1) / 2) * (size - 1): the halving is exact, so the product with hf = (size - 1) / 2 (also exact) rounds the
+  // same real number once: the same float as the reference's two multiplications (grid_raytracing.cpp:8-11)
+  p.x = (p.x + 1.0f) * g.hfx; p.y = (p.y + 1.0f) * g.hfy; p.z = (p.z + 1.0f) * g.hfz;
   const float c0fx = floorf(p.x), c0fy = floorf(p.y), c0fz = floorf(p.z);
   const uint32_t c0x = (uint32_t)c0fx, c0y = (uint32_t)c0fy, c0z = (uint32_t)c0fz;
   const bool ix = p.x != c0fx, iy = p.y != c0fy, iz = p.z != c0fz;  // c1 != c0 on that axis

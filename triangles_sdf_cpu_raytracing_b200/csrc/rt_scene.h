@@ -18,6 +18,7 @@ struct GridDev {
   uint32_t bricks;              // 0 linear, 1 bricked
   uint32_t stride_x, stride_y;  // linear: sy*sz, sz;  bricked: nby*nbz*512, nbz*512 (elements)
   float fx, fy, fz;             // (float)(size - 1), grid_raytracing.cpp:9-11
+  float hfx, hfy, hfz;          // (float)(size - 1) / 2, exact
 };
 
 // ---- SDF octree (replaces SDFOctree, octree_raytracing.hpp:8-47) ----------------------------------------

@@ -381,6 +381,11 @@ def run_cuda(args):
         barrier()
         if shared is not None:
             shared.close()
+    staged = int(rt.lib().rt_staged_launch_count())
+    if world > 1:  # ranks != 0 are the ones that store into a peer framebuffer
+        tt = torch.tensor([staged], device=dev, dtype=torch.int64)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        staged = int(tt.item())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -497,6 +502,7 @@ def run_cuda(args):
         "config": {"workload": args.scene, "scene": scene_name, "width": W, "height": H, "shading": "Normal",
                    "math": args.math, "sched": args.sched, "grid_layout": args.grid_layout,
                    "scene_bytes": scene.info()["device_bytes"], "scene_build_s": round(t_build, 3),
+                   "staged_peer_store_launches": staged,
                    "mesh_accel": args.mesh_accel, "mesh": scene.mesh_stats() if kind == "mesh" else None, "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB write)",
                    "partition": "whole frame" if world == 1 else
                    f"{band_rows}-row bands interleaved over {world} GPUs, " +

@@ -67,6 +67,7 @@ SIGNATURES = {
     "rt_ipc_export": (_i, [_vp, C.c_char_p]),
     "rt_ipc_open": (_i, [C.c_char_p, _pp]),
     "rt_ipc_close": (_i, [_vp]),
+    "rt_staged_launch_count": (C.c_uint64, []),
     "rt_memcpy_d2h": (_i, [_vp, _vp, C.c_uint64, _vp]),
     "rt_memcpy_h2d": (_i, [_vp, _vp, C.c_uint64, _vp]),
     # include/rt_b200_host.h

@@ -23,6 +23,17 @@ namespace {
 thread_local std::string g_err;
 std::atomic<int> g_math{RT_MATH_EXACT};
 std::atomic<int> g_sched{RT_SCHED_AUTO};
+// Device pointers obtained through rt_ipc_open: another GPU's memory mapped into this process.  (The runtime reports
+// the mapping device, not the owner, for such pointers, so the library remembers them itself.)
+std::mutex g_peer_mu;
+std::vector<const void *> g_peer_ptrs;
+std::atomic<uint64_t> g_staged_launches{0};
+bool is_peer_pointer(const void *p) {
+  std::lock_guard<std::mutex> lock(g_peer_mu);
+  for (const void *q : g_peer_ptrs)
+    if (q == p) return true;
+  return false;
+}
 
 int fail(int code, const std::string &msg) {
   g_err = msg;
@@ -442,14 +453,10 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   int sched = resolve_sched(scene);
   if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && g_env_stage != 0) {
     bool peer = g_env_stage == 1;
-    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20)) {  // measured on 8 GPUs: pays at 4K, not at 1080p
-      cudaPointerAttributes pa;
-      if (cudaPointerGetAttributes(&pa, color) == cudaSuccess)
-        peer = pa.type == cudaMemoryTypeDevice && pa.device != scene->device;
-      else
-        cudaGetLastError();
-    }
+    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20))  // measured on 8 GPUs: pays at 4K, not at 1080p
+      peer = is_peer_pointer(color) && is_peer_pointer(t_out);
     a.stage_stores = peer ? 1 : 0;
+    if (peer) g_staged_launches.fetch_add(1);
     // the staged stores live in the tiles kernel: for a peer framebuffer the octree's default (persistent, ~1 % faster
     // on one GPU) gives way to it
     if (peer && g_sched.load() == RT_SCHED_AUTO) sched = RT_SCHED_TILES;
@@ -665,10 +672,24 @@ int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dev_ptr)
   std::memcpy(&h, handle, sizeof h);
   *dev_ptr = nullptr;
   RT_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  {
+    std::lock_guard<std::mutex> lock(g_peer_mu);
+    g_peer_ptrs.push_back(*dev_ptr);
+  }
   return RT_OK;
 }
 
+uint64_t rt_staged_launch_count(void) { return g_staged_launches.load(); }
+
 int rt_ipc_close(void *dev_ptr) {
+  {
+    std::lock_guard<std::mutex> lock(g_peer_mu);
+    for (size_t i = 0; i < g_peer_ptrs.size(); ++i)
+      if (g_peer_ptrs[i] == dev_ptr) {
+        g_peer_ptrs.erase(g_peer_ptrs.begin() + (long)i);
+        break;
+      }
+  }
   RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
   return RT_OK;
 }

@@ -5,7 +5,8 @@ mkdir -p gpurun_out
 python bench.py --steps 5 --warmup 3 > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_grid65_1080p.csv \
     python bench.py --steps 5 --warmup 3 > gpurun_out/ncu_launches.log 2>&1
-for s in grid65_1080p grid513_4k octree6_4k octree8_4k bunny_4k bunny_s2_4k cube_512; do
+SCENES=${SCENES:-"grid65_1080p grid513_4k octree6_4k octree8_4k bunny_4k bunny_s2_4k cube_512"}
+for s in $SCENES; do
   python bench.py --scene $s --steps 5 --warmup 3 > gpurun_out/plain_$s.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:render -s 3 -c 1 -f -o gpurun_out/prof_$s \
       python bench.py --scene $s --steps 5 --warmup 3 > gpurun_out/ncu_full_$s.log 2>&1

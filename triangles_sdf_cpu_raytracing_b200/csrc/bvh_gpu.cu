@@ -356,9 +356,18 @@ bool build_bvh8_device(const float *vpos4, uint32_t n_verts, const uint32_t *ind
     err = why;
     return false;
   };
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0);
-  cudaEventCreate(&e1);
+  struct Events {  // destroyed on every exit path
+    cudaEvent_t a = nullptr, b = nullptr;
+    Events() {
+      cudaEventCreate(&a);
+      cudaEventCreate(&b);
+    }
+    ~Events() {
+      cudaEventDestroy(a);
+      cudaEventDestroy(b);
+    }
+  } ev;
+  cudaEvent_t e0 = ev.a, e1 = ev.b;
   cudaError_t ce = cudaMemcpy(dV, vpos4, (size_t)n_verts * 16, cudaMemcpyHostToDevice);
   if (ce == cudaSuccess) ce = cudaMemcpy(dI, indices, (size_t)n_indices * 4, cudaMemcpyHostToDevice);
   BuildState h;
@@ -410,8 +419,6 @@ bool build_bvh8_device(const float *vpos4, uint32_t n_verts, const uint32_t *ind
   if (ce != cudaSuccess) return bail(std::string("device BVH build: ") + cudaGetErrorString(ce));
   cudaMemcpy(&h, st, sizeof h, cudaMemcpyDeviceToHost);
   cudaEventElapsedTime(&out.build_ms, e0, e1);
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   if (h.error == 1u) return bail("mesh index out of range");
   if (h.error == 2u) return bail("device BVH build: wide node pool exhausted");
   // the traversal pushes at most 8 children per visited level and pops one before descending

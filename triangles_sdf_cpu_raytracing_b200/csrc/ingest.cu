@@ -140,9 +140,18 @@ int ingest_octree_device(const void *nodes36, uint32_t n, uint32_t **linkOut, fl
     err = why;
     return code;
   };
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0);
-  cudaEventCreate(&e1);
+  struct Events {  // destroyed on every exit path
+    cudaEvent_t a = nullptr, b = nullptr;
+    Events() {
+      cudaEventCreate(&a);
+      cudaEventCreate(&b);
+    }
+    ~Events() {
+      cudaEventDestroy(a);
+      cudaEventDestroy(b);
+    }
+  } ev;
+  cudaEvent_t e0 = ev.a, e1 = ev.b;
   cudaError_t ce = cudaMemcpy(raw, nodes36, (size_t)n * 36, cudaMemcpyHostToDevice);
   if (ce == cudaSuccess) ce = cudaMemset(seen, 0, (size_t)n * 4);
   WalkState h = {0u, {1u, 0u}};
@@ -175,8 +184,6 @@ int ingest_octree_device(const void *nodes36, uint32_t n, uint32_t **linkOut, fl
   if (ce == cudaSuccess) ce = cudaGetLastError();
   if (ce != cudaSuccess) return bail(INGEST_CUDA, std::string("octree ingestion: ") + cudaGetErrorString(ce));
   if (ms) cudaEventElapsedTime(ms, e0, e1);
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   *linkOut = link;
   *valuesOut = values;
   *depthOut = depth;

@@ -187,7 +187,7 @@ int rt_device_free(void *dev_ptr);
 int rt_ipc_export(const void *dev_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]);
 int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dev_ptr); /* enables peer access lazily */
 /* number of render launches so far that stored their tiles into a peer framebuffer (a pointer from rt_ipc_open) as
- * shared-memory staged 128-byte TMA bulk writes (frames of >= 3 Mpixel split over >= 4 ranks, rt_frame.clear = 1, W % 8 == 0) */
+ * shared-memory staged 128-byte TMA bulk writes (frames of >= 3 Mpixel split over >= 8 ranks, rt_frame.clear = 1, W % 8 == 0) */
 uint64_t rt_staged_launch_count(void);
 int rt_ipc_close(void *dev_ptr);
 /* stream-ordered copies between host and device buffers (stream = cudaStream_t as void*, NULL = default stream;

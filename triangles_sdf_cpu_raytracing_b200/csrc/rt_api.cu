@@ -453,9 +453,11 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   int sched = resolve_sched(scene);
   if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && g_env_stage != 0) {
     bool peer = g_env_stage == 1;
-    // measured: pays when rank 0's inbound NVLink is the bottleneck (8 GPUs, 4K: 0.139 -> 0.096 ms), not at 1080p
-    // (0.051 -> 0.053 ms) and not on 2 GPUs (4K: 0.196 -> 0.214 ms, the 32 x 4 block with its barrier is a slower kernel)
-    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 4u)
+    // measured (profiles/r1_multi/TABLE.txt): pays when rank 0's inbound NVLink is saturated, i.e. on 8 GPUs at 4K
+    // (grid 0.139 -> 0.096 ms, bunny 0.147 -> 0.125 ms); not at 1080p (0.051 -> 0.053 ms), mixed on 4 GPUs (grid 0.131 ->
+    // 0.124, bunny 0.139 -> 0.165 ms) and slower on 2 (grid 0.196 -> 0.214 ms): the 32 x 4 block with its barrier is a
+    // slower kernel than the 16 x 8 one
+    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
       peer = is_peer_pointer(color) && is_peer_pointer(t_out);
     a.stage_stores = peer ? 1 : 0;
     if (peer) g_staged_launches.fetch_add(1);

@@ -54,3 +54,36 @@ def test_argument_validation_reports_errors():
     assert lib.rt_set_math_mode(7) == -1
     assert lib.rt_set_sched_mode(-1) == -1
     assert lib.rt_scene_kind_of(None) == -1
+
+
+def test_headers_are_plain_c(tmp_path):
+    """The boundary is a C ABI: both headers compile as C99 with no C++ / CUDA / torch types, and a C program links
+    against the library using only what they declare."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if not cc:
+        pytest.skip("no C compiler")
+    src = tmp_path / "abi.c"
+    src.write_text("""
+#include <stdio.h>
+#include "rt_b200.h"
+#include "rt_b200_host.h"
+int main(void) {
+  rt_frame f;
+  rt_counters c;
+  int n = -1;
+  (void)f; (void)c;
+  printf("%s %d %d %d\\n", rt_version(), (int)sizeof(rt_frame), (int)sizeof(rt_counters), rt_device_count(&n) == RT_OK ? n : -1);
+  return rt_set_math_mode(RT_MATH_EXACT) == RT_OK && rt_set_sched_mode(RT_SCHED_COMPACT) == RT_OK &&
+         rt_set_sched_mode(RT_SCHED_AUTO) == RT_OK ? 0 : 1;
+}
+""")
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    r = subprocess.run([cc, "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src),
+                        "-o", str(exe), "-L", libdir, "-lrt_b200", f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.split()[-3:-1] == [str(C.sizeof(rt.RtFrame)), str(C.sizeof(rt.RtCounters))]

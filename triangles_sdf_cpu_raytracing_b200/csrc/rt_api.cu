@@ -475,13 +475,16 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
 }
 
 int ensure_host_buffers(rt_scene *s, size_t pixels) {
-  if (!s->h_stream) {
-    RT_CUDA(cudaStreamCreateWithFlags(&s->h_stream, cudaStreamNonBlocking));
-    RT_CUDA(cudaStreamCreateWithFlags(&s->h_up, cudaStreamNonBlocking));
-    RT_CUDA(cudaStreamCreateWithFlags(&s->h_down, cudaStreamNonBlocking));
-    for (auto &e : s->ev) RT_CUDA(cudaEventCreate(&e));
-    for (auto &e : s->ev_up) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    for (auto &e : s->ev_k) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  if (!s->h_cnt) {  // created last: a call that failed half-way is completed by the next one
+    if (!s->h_stream) RT_CUDA(cudaStreamCreateWithFlags(&s->h_stream, cudaStreamNonBlocking));
+    if (!s->h_up) RT_CUDA(cudaStreamCreateWithFlags(&s->h_up, cudaStreamNonBlocking));
+    if (!s->h_down) RT_CUDA(cudaStreamCreateWithFlags(&s->h_down, cudaStreamNonBlocking));
+    for (auto &e : s->ev)
+      if (!e) RT_CUDA(cudaEventCreate(&e));
+    for (auto &e : s->ev_up)
+      if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : s->ev_k)
+      if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     RT_CUDA(cudaMalloc(&s->h_cnt, sizeof(rt_counters)));
   }
   if (pixels > s->h_pixels) {
@@ -528,6 +531,17 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   rc = ensure_host_buffers(s, pixels);
   if (rc) return rc;
   cudaStream_t st = s->h_stream;
+  // An error return must not leave copies into the caller's buffers in flight: drain the three streams on the way out.
+  struct Drain {
+    rt_scene *s;
+    bool armed = true;
+    ~Drain() {
+      if (!armed) return;
+      cudaStreamSynchronize(s->h_up);
+      cudaStreamSynchronize(s->h_stream);
+      cudaStreamSynchronize(s->h_down);
+    }
+  } drain{s};
   // The frame is cut into row chunks that flow through three streams: upload (only when the caller's depth /
   // colour matter: the framebuffer is in/out, raytracing.cpp:17,90-94), render, download.  The PCIe copies of one
   // chunk overlap the kernel of the next, so the call costs ~max(copy time, kernel time), not their sum.
@@ -594,6 +608,7 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   RT_CUDA(cudaStreamSynchronize(s->h_down));
   if (device_ms) RT_CUDA(cudaEventElapsedTime(device_ms, s->ev[1], s->ev[2]));
   if (total_ms) RT_CUDA(cudaEventElapsedTime(total_ms, s->ev[0], s->ev[3]));
+  drain.armed = false;  // both syncs above succeeded: nothing is pending
   return RT_OK;
 }
 

@@ -446,10 +446,16 @@ def run_cuda(args):
                "h2d_bytes_per_step": C.sizeof(L.RtFrame), "d2h_bytes_per_step": 8 * px,
                "api": "rt_render_host, rt_frame.clear=1 (FrameBuffer::clear + Renderer::draw in one call), pinned host "
                       "framebuffer left untouched by the CPU between calls",
+               "transfer": ("pipelined copy-engine downloads (RT_HOST_ZEROCOPY=0)"
+                            if os.environ.get("RT_HOST_ZEROCOPY", "2") == "0" or W % 8 or args.scene == "cube_512"
+                            or args.sched in ("persistent", "compact") else
+                            "the render kernel stores its tiles into the pinned host framebuffer over PCIe "
+                            "(128-byte bulk stores, one launch, no copy engine)"),
                "d2h_floor_ms_at_56GBps": 8 * px / 56e9 * 1e3,
                "after_cpu_read_of_colour": {"value": px / blit_ms / 1e3, "ms_per_step": blit_ms},
                "after_cpu_rewrite_of_both_buffers": {"value": px / dirty_ms / 1e3, "ms_per_step": dirty_ms,
-                                                     "note": "dirty CPU cache lines slow the DMA writes"},
+                                                     "note": "dirty CPU cache lines slow copy-engine writes (0.40 -> 0.58 ms at 1080p, "
+                                                             "profiles/r1_e2e_ab.txt); the kernel's own stores are not affected"},
                "inout": {"value": px / inout_ms / 1e3, "ms_per_step": inout_ms, "h2d_bytes_per_step": 8 * px,
                          "d2h_bytes_per_step": 8 * px,
                          "api": "rt_render_host, in/out framebuffer cleared on the host before each call (raytracing.cpp:17,90-94)"}}

@@ -164,7 +164,12 @@ int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *col
 /* Host framebuffer, synchronous, exactly the reference's call: copies t in, renders, copies colour / t
  * (/ prim) out.  Returns the device time of the render kernels alone in *device_ms (the reference returns
  * its own stopwatch, raytracing.cpp:97-101) and of the whole call incl. copies in *total_ms.  Any of prim,
- * device_ms, total_ms, counters may be NULL. */
+ * device_ms, total_ms, counters may be NULL.
+ * Page-locked framebuffer: when color and t_inout are pinned host memory (rt_pinned_alloc / rt_pinned_register below, or
+ * any cudaHostAlloc / cudaHostRegister memory), rt_frame.clear = 1, the whole frame is rendered (band_count <= 1),
+ * W % 8 == 0 and prim / counters are NULL, the kernel stores its tiles straight into the caller's buffers over PCIe
+ * (128-byte bulk stores, no device framebuffer, no copy engine); *device_ms then equals *total_ms.  Pageable buffers
+ * and every other combination go through the pipelined copies. */
 int rt_render_host(const rt_scene *scene, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
                    float *device_ms, float *total_ms, rt_counters *counters);
 
@@ -190,6 +195,15 @@ int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dev_ptr)
  * shared-memory staged 128-byte TMA bulk writes (frames of >= 3 Mpixel split over >= 8 ranks, rt_frame.clear = 1, W % 8 == 0) */
 uint64_t rt_staged_launch_count(void);
 int rt_ipc_close(void *dev_ptr);
+/* Page-locked host memory for the framebuffers of rt_render_host.  rt_pinned_register pins an existing range in place:
+ * the reference's FrameBuffer keeps its Image2D<uint32_t> color / Image2D<float> t (src/raytracing.hpp:9-15, storage
+ * Image2d.h:91) and registers their data() once after FrameBuffer::resize.  Two ranges registered separately must
+ * not share a memory page (frame-sized vectors are mmap'd by the allocator and never do; tiny ones may: use
+ * rt_pinned_alloc for those). */
+int rt_pinned_alloc(uint64_t bytes, void **host_ptr);
+int rt_pinned_free(void *host_ptr);
+int rt_pinned_register(void *host_ptr, uint64_t bytes);
+int rt_pinned_unregister(void *host_ptr);
 /* stream-ordered copies between host and device buffers (stream = cudaStream_t as void*, NULL = default stream;
  * the call returns after the copy has completed) */
 int rt_memcpy_d2h(void *host, const void *dev_ptr, uint64_t bytes, void *stream);

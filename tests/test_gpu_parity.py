@@ -309,3 +309,87 @@ print("staged ok")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "staged ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["0", "1", "2"])
+def test_host_zero_copy_is_bit_exact(mode):
+    """rt_render_host on a pinned host framebuffer, every transfer mode (RT_HOST_ZEROCOPY: 0 = pipelined copies,
+    1 = plain stores into host memory, 2 = staged 128-byte bulk stores, the default).  Dirty buffers, fused clear: every
+    pixel must come back as the reference's.  The knob is read once at load, so the check runs in its own process."""
+    import os
+    import subprocess
+    import sys
+    code = """
+import ctypes as C
+import numpy as np, torch
+import triangles_sdf_cpu_raytracing_b200 as rt
+from triangles_sdf_cpu_raytracing_b200 import _lib as L
+from tests import util
+g = util.Golden()
+for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "stanford-bunny|default|160x90", "sdf_6|orbit23tilt|96x64",
+            "cube|default|128x128"):
+    c = g.case(key)
+    s = util.cuda_scene(g, c["scene"])
+    W, H = c["W"], c["H"]
+    color = torch.full((H * W,), 0x5A5A5A5A, dtype=torch.int32).pin_memory()
+    t = torch.full((H * W,), 0.25, dtype=torch.float32).pin_memory()
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True)
+    dms, tms = C.c_float(), C.c_float()
+    for _ in range(2):
+        L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(color.data_ptr()), C.c_void_p(t.data_ptr()), None,
+                                       C.byref(dms), C.byref(tms), None))
+    assert tms.value > 0.0
+    assert util.same_bits(t.numpy().reshape(H, W), c["t"]), key
+    assert np.array_equal(color.numpy().view(np.uint32).reshape(H, W), c["color_normal"]), key
+print("zero-copy ok")
+"""
+    env = dict(os.environ, RT_HOST_ZEROCOPY=mode)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "zero-copy ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_pinned_framebuffer_and_registered_arrays():
+    """The page-locked framebuffer API (rt_pinned_alloc / rt_pinned_register, include/rt_b200.h): PinnedFrameBuffer +
+    Scene.render_into with the fused clear (kernel stores into host memory) and with the reference's in/out contract
+    (copies), and numpy arrays registered in place."""
+    import ctypes as C
+    from triangles_sdf_cpu_raytracing_b200 import _lib as L
+    for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "stanford-bunny|default|160x90"):
+        c = G.case(key)
+        s = util.cuda_scene(G, c["scene"])
+        W, H = c["W"], c["H"]
+        fb = rt.PinnedFrameBuffer(W, H)
+        fb.color[...] = 0x5A5A5A5A
+        fb.t[...] = 0.25
+        dms, tms = s.render_into(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True), fb)
+        assert tms > 0.0
+        assert util.same_bits(fb.t, c["t"]) and np.array_equal(fb.color, c["color_normal"]), key
+        fb.clear()
+        s.render_into(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), fb)
+        assert util.same_bits(fb.t, c["t"]) and np.array_equal(fb.color, c["color_normal"]), key
+        # in/out: a nearer depth already in the buffer wins (raytracing.cpp:90-94)
+        fb.color[...] = 7
+        fb.t[...] = 1e-3
+        s.render_into(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), fb)
+        assert np.all(fb.color == 7) and np.all(fb.t == np.float32(1e-3)), key
+        fb.free()
+        def own_pages(dtype):  # two registered ranges must not share a page: page-aligned, padded to whole pages
+            raw = np.empty(H * W * 4 + 8192, np.uint8)
+            off = (-raw.ctypes.data) % 4096
+            return raw[off:off + H * W * 4].view(dtype).reshape(H, W)
+        color, t = own_pages(np.uint32), own_pages(np.float32)
+        color[...] = 0x5A5A5A5A
+        t[...] = 0.25
+        L.check(L.lib().rt_pinned_register(C.c_void_p(color.ctypes.data), color.nbytes))
+        L.check(L.lib().rt_pinned_register(C.c_void_p(t.ctypes.data), t.nbytes))
+        try:
+            f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True)
+            L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(color.ctypes.data), C.c_void_p(t.ctypes.data),
+                                           None, None, None, None))
+        finally:
+            L.check(L.lib().rt_pinned_unregister(C.c_void_p(color.ctypes.data)))
+            L.check(L.lib().rt_pinned_unregister(C.c_void_p(t.ctypes.data)))
+        assert util.same_bits(t, c["t"]) and np.array_equal(color, c["color_normal"]), key

@@ -122,6 +122,11 @@ def test_cpp_frame_loop_reproduces_the_reference_frames(tmp_path):
     color = raw[:4 * 96 * 64].view(np.uint32).reshape(64, 96)
     t = raw[4 * 96 * 64:].view(np.float32).reshape(64, 96)
     assert util.same_bits(t, c["t"]) and np.array_equal(color, c["color_normal"])
+    # the same loop on a page-locked framebuffer (FrameBuffer::pin + frameIsCleared): the kernel writes host memory
+    p = subprocess.run([exe] + exe_args + [str(tmp_path / "o5p.raw"), "5", "pinned"], capture_output=True, text=True,
+                       timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert open(tmp_path / "o5p.raw", "rb").read() == open(tmp_path / "o5.raw", "rb").read()
 
 
 def test_cpp_frame_loop_obj_mesh(tmp_path):

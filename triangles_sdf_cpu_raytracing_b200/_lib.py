@@ -68,6 +68,10 @@ SIGNATURES = {
     "rt_ipc_open": (_i, [C.c_char_p, _pp]),
     "rt_ipc_close": (_i, [_vp]),
     "rt_staged_launch_count": (C.c_uint64, []),
+    "rt_pinned_alloc": (_i, [C.c_uint64, _pp]),
+    "rt_pinned_free": (_i, [_vp]),
+    "rt_pinned_register": (_i, [_vp, C.c_uint64]),
+    "rt_pinned_unregister": (_i, [_vp]),
     "rt_memcpy_d2h": (_i, [_vp, _vp, C.c_uint64, _vp]),
     "rt_memcpy_h2d": (_i, [_vp, _vp, C.c_uint64, _vp]),
     # include/rt_b200_host.h

@@ -38,6 +38,41 @@ def make_frame(ray_pos, view_inv, proj_inv, W, H, mode=L.SHADE_NORMAL, light=(2.
     return f
 
 
+class PinnedFrameBuffer:
+    """FrameBuffer (raytracing.hpp:9-20) in page-locked host memory: `color` [H,W] uint32 and `t` [H,W] float32 are
+    numpy views of rt_pinned_alloc memory, so Scene.render_into stores its tiles straight into them (rt_b200.h,
+    rt_render_host).  Keep the object alive while the views are in use."""
+
+    def __init__(self, W: int, H: int):
+        self.W, self.H = int(W), int(H)
+        n = self.W * self.H * 4
+        self._pc, self._pt = C.c_void_p(), C.c_void_p()
+        L.check(L.lib().rt_pinned_alloc(n, C.byref(self._pc)))
+        L.check(L.lib().rt_pinned_alloc(n, C.byref(self._pt)))
+        self.color = np.ctypeslib.as_array((C.c_uint32 * (self.W * self.H)).from_address(self._pc.value)).reshape(H, W)
+        self.t = np.ctypeslib.as_array((C.c_float * (self.W * self.H)).from_address(self._pt.value)).reshape(H, W)
+        self.clear()
+
+    def clear(self):
+        """FrameBuffer::clear (raytracing.hpp:16-19)."""
+        self.color[...] = 0
+        self.t[...] = np.inf
+
+    def free(self):
+        for name in ("_pc", "_pt"):
+            p = getattr(self, name, None)
+            if p is not None and p.value:
+                L.lib().rt_pinned_free(p)
+                setattr(self, name, None)
+        self.color = self.t = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
 class Scene:
     """An uploaded, immutable scene (rt_scene*)."""
 
@@ -94,6 +129,13 @@ class Scene:
                                        C.byref(tms), C.byref(cnt) if cnt is not None else None))
         return dict(color=color, t=t, prim=prim, device_ms=dms.value, total_ms=tms.value,
                     counters=cnt.as_dict() if cnt is not None else None)
+
+    def render_into(self, frame: L.RtFrame, fb: PinnedFrameBuffer):
+        """Renderer::draw into a page-locked framebuffer, in place -> (device_ms, total_ms)."""
+        assert (fb.H, fb.W) == (frame.height, frame.width)
+        dms, tms = C.c_float(), C.c_float()
+        L.check(L.lib().rt_render_host(self._h, C.byref(frame), fb._pc, fb._pt, None, C.byref(dms), C.byref(tms), None))
+        return float(dms.value), float(tms.value)
 
     # ---- Renderer::draw on device-resident framebuffers (torch tensors or raw pointers), asynchronous
     def render_device(self, frame: L.RtFrame, color_ptr: int, t_in_ptr, t_out_ptr: int, prim_ptr=None,

@@ -421,6 +421,14 @@ int env_int(const char *name) {
 const int g_env_tile_block = env_int("RT_TILE_BLOCK");
 const int g_env_host_chunks = env_int("RT_HOST_CHUNKS");
 const int g_env_stage = std::getenv("RT_STAGE_STORES") ? env_int("RT_STAGE_STORES") : -1;  // -1: peer framebuffers only
+// RT_HOST_ZEROCOPY: rt_render_host with a pinned host framebuffer; 0 = copy pipeline, 1 = kernel stores straight into the
+// host buffers, 2 = the same through the staged 128-byte bulk stores.  Unset = 2, by measurement (profiles/r1_e2e_ab.txt,
+// B200, PCIe Gen5): 1080p 0.397 -> 0.346 ms, and 0.58 -> 0.35 ms when the CPU has just rewritten the buffers (the
+// reference clears on the host before every draw: dirty cache lines slow the copy engine's writes, not these);
+// 4K 1.235 -> 1.295 ms untouched, 1.60 -> 1.31 ms rewritten.  Plain 32-byte stores (1) are 1.7x slower than the copies;
+// 256-byte bulk stores measured the same as 128-byte ones.
+constexpr int HOST_ZEROCOPY_DEFAULT = 2;
+const int g_env_zero_copy = std::getenv("RT_HOST_ZEROCOPY") ? env_int("RT_HOST_ZEROCOPY") : HOST_ZEROCOPY_DEFAULT;
 const int g_env_oct_refill = env_int("RT_OCT_REFILL");
 const int g_env_oct_batch = env_int("RT_OCT_BATCH");
 
@@ -435,7 +443,7 @@ int resolve_sched(const rt_scene *s) {
 }
 
 int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color, const float *t_in, float *t_out,
-                     uint32_t *prim, rt_counters *counters_dev, cudaStream_t st) {
+                     uint32_t *prim, rt_counters *counters_dev, cudaStream_t st, int force_stage = -1) {
   RenderArgs a;
   a.scene = scene->dev;
   a.frame = fd;
@@ -451,8 +459,8 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   // 128-byte TMA bulk writes.  Needs the fused clear (whole tiles are written) and 32-byte-multiple rows.
   a.stage_stores = 0;
   int sched = resolve_sched(scene);
-  if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && g_env_stage != 0) {
-    bool peer = g_env_stage == 1;
+  if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && (force_stage >= 0 ? force_stage == 1 : g_env_stage != 0)) {
+    bool peer = g_env_stage == 1 || force_stage == 1;
     // measured (profiles/r1_multi/TABLE.txt): pays when rank 0's inbound NVLink is saturated, i.e. on 8 GPUs at 4K
     // (grid 0.139 -> 0.096 ms, bunny 0.147 -> 0.125 ms); not at 1080p (0.051 -> 0.053 ms), mixed on 4 GPUs (grid 0.131 ->
     // 0.124, bunny 0.139 -> 0.165 ms) and slower on 2 (grid 0.196 -> 0.214 ms): the 32 x 4 block with its barrier is a
@@ -460,7 +468,7 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
     if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
       peer = is_peer_pointer(color) && is_peer_pointer(t_out);
     a.stage_stores = peer ? 1 : 0;
-    if (peer) g_staged_launches.fetch_add(1);
+    if (peer && force_stage < 0) g_staged_launches.fetch_add(1);  // counts the multi-GPU path only
     // the staged stores live in the tiles kernel: for a peer framebuffer the octree's default (persistent, ~1 % faster
     // on one GPU) gives way to it
     if (peer && g_sched.load() == RT_SCHED_AUTO) sched = RT_SCHED_TILES;
@@ -472,6 +480,16 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
                                                   : exact::launch_render(a, sched, scene->sm_count, st);
   if (e != cudaSuccess) return cuda_fail(e, "render launch");
   return RT_OK;
+}
+
+// Device-side address of a pinned (page-locked, mapped) host buffer, or null for pageable / device memory.
+void *mapped_host_pointer(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
 }
 
 int ensure_host_buffers(rt_scene *s, size_t pixels) {
@@ -542,6 +560,32 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
       cudaStreamSynchronize(s->h_down);
     }
   } drain{s};
+  // Pinned host framebuffer, whole frame overwritten, nothing else asked for: the kernel stores its tiles straight into
+  // the caller's buffers over PCIe (no device framebuffer, no copy engine, one launch).
+  // (mode 2 needs the launch to be the staged tiles kernel: primary rays, not the brute-force mesh, tiles scheduling;
+  // everything else keeps the copies, which beat plain 32-byte stores over PCIe)
+  const bool secondary = fd.mode == RT_SHADE_LAMBERT && (fd.shadows || fd.reflections);
+  const int sched_now = g_sched.load();
+  const bool staged_ok = !secondary && !(s->kind == RT_SCENE_MESH && s->dev.mesh.brute) &&
+                         (sched_now == RT_SCHED_AUTO || sched_now == RT_SCHED_TILES);
+  if (g_env_zero_copy != 0 && (g_env_zero_copy == 1 || staged_ok) && fd.band_count <= 1 && fd.clear && !prim &&
+      !counters && fd.W % 8u == 0u) {
+    uint32_t *dc = static_cast<uint32_t *>(mapped_host_pointer(color));
+    float *dt = static_cast<float *>(mapped_host_pointer(t_inout));
+    if (dc && dt) {
+      RT_CUDA(cudaEventRecord(s->ev[0], st));
+      rc = render_on_stream(s, fd, dc, nullptr, dt, nullptr, nullptr, st, g_env_zero_copy >= 2 ? 1 : 0);
+      if (rc) return rc;
+      RT_CUDA(cudaEventRecord(s->ev[3], st));
+      RT_CUDA(cudaStreamSynchronize(st));
+      float ms = 0.0f;
+      if (device_ms || total_ms) RT_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[3]));
+      if (device_ms) *device_ms = ms;
+      if (total_ms) *total_ms = ms;
+      drain.armed = false;
+      return RT_OK;
+    }
+  }
   // The frame is cut into row chunks that flow through three streams: upload (only when the caller's depth /
   // colour matter: the framebuffer is in/out, raytracing.cpp:17,90-94), render, download.  The PCIe copies of one
   // chunk overlap the kernel of the next, so the call costs ~max(copy time, kernel time), not their sum.
@@ -710,6 +754,32 @@ int rt_ipc_close(void *dev_ptr) {
       }
   }
   RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  return RT_OK;
+}
+
+// ---- page-locked host framebuffers (rt_render_host stores straight into them) -------------------------------------
+int rt_pinned_alloc(uint64_t bytes, void **host_ptr) {
+  if (!host_ptr) return fail(RT_ERR_INVALID, "host_ptr is null");
+  *host_ptr = nullptr;
+  RT_CUDA(cudaHostAlloc(host_ptr, bytes ? bytes : 1, cudaHostAllocPortable | cudaHostAllocMapped));
+  return RT_OK;
+}
+
+int rt_pinned_free(void *host_ptr) {
+  if (!host_ptr) return RT_OK;
+  RT_CUDA(cudaFreeHost(host_ptr));
+  return RT_OK;
+}
+
+int rt_pinned_register(void *host_ptr, uint64_t bytes) {
+  if (!host_ptr || bytes == 0) return fail(RT_ERR_INVALID, "null or empty host range");
+  RT_CUDA(cudaHostRegister(host_ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+  return RT_OK;
+}
+
+int rt_pinned_unregister(void *host_ptr) {
+  if (!host_ptr) return RT_OK;
+  RT_CUDA(cudaHostUnregister(host_ptr));
   return RT_OK;
 }
 

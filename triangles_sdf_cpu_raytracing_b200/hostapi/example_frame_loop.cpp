@@ -1,5 +1,6 @@
 // The viewer's frame loop (src/main.cpp:89-91, 196-208) without the window: same classes, same calls.
-//   example_frame_loop <scene.grid|.octree|.obj> <W> <H> <normal|lambert|color> <plane 0|1> <out.raw> [orbit steps]
+//   example_frame_loop <scene.grid|.octree|.obj> <W> <H> <normal|lambert|color> <plane 0|1> <out.raw> [orbit steps [pinned]]
+// "pinned": FrameBuffer::pin() + Renderer::frameIsCleared, the page-locked framebuffer the kernel stores straight into.
 // out.raw = W*H uint32 colour followed by W*H float depth (the FrameBuffer contents after draw).
 // An output name ending in .ppm writes the colour buffer as a binary PPM instead (the headless stand-in for the
 // viewer's SDL blit, main.cpp:238-249); with orbit steps one file per frame: name_000.ppm, name_001.ppm, ...
@@ -45,6 +46,7 @@ int main(int argc, char **argv) {
     const std::string mode = argv[4];
     const bool plane = std::atoi(argv[5]) != 0;
     const int orbit = argc > 7 ? std::atoi(argv[7]) : 0;
+    const bool pinned = argc > 8 && std::strcmp(argv[8], "pinned") == 0;
     const std::string outName = argv[6];
     const bool ppm = ends_with(outName, ".ppm");
 
@@ -76,6 +78,10 @@ int main(int argc, char **argv) {
     renderer.shadingMode = mode == "normal" ? ShadingMode::Normal : mode == "color" ? ShadingMode::Color : ShadingMode::Lambert;
     renderer.enableShadows = plane;
     renderer.enableReflections = plane;
+    if (pinned) {
+      frameBuf.pin();
+      renderer.frameIsCleared = true;  // clear() below runs right before every draw (main.cpp:197)
+    }
 
     float time = 0.0f;
     for (int frame = 0; frame <= orbit; ++frame) {

@@ -7,6 +7,7 @@
 // Every class here is a thin owner of an `rt_scene*` / host framebuffer; all arithmetic on rays happens in the CUDA
 // kernels behind include/rt_b200.h.  There is no CPU fallback: without a device the constructors / draw throw.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <limits>
 #include <memory>
@@ -25,25 +26,50 @@ inline void check(int rc, const char *what) {
 }
 }  // namespace rthost
 
-// LiteImage::Image2D<T> subset used by FrameBuffer (Image2d.h:67-107): row-major, index y*width + x
+// LiteImage::Image2D<T> subset used by FrameBuffer (Image2d.h:67-107): row-major, index y*width + x.
+// B200 extension: pin() moves the pixels into page-locked memory (rt_pinned_alloc) and keeps them there across resizes.
 template <typename T> class Image2D {
 public:
+  Image2D() = default;
+  Image2D(const Image2D &) = delete;  // owns a page-locked block
+  Image2D &operator=(const Image2D &) = delete;
+  ~Image2D() { release(); }
   void resize(uint32_t w, uint32_t h) {
+    const bool wasPinned = m_pinned != nullptr;
+    release();
     m_w = w;
     m_h = h;
-    m_data.resize(static_cast<size_t>(w) * h);
+    if (wasPinned) allocPinned();
+    else m_data.resize(count());
   }
-  void clear(T v) { std::fill(m_data.begin(), m_data.end(), v); }
+  void clear(T v) { std::fill(data(), data() + count(), v); }
   uint32_t width() const { return m_w; }
   uint32_t height() const { return m_h; }
-  T *data() { return m_data.data(); }
-  const T *data() const { return m_data.data(); }
-  T &operator[](size_t i) { return m_data[i]; }
-  const T &operator[](size_t i) const { return m_data[i]; }
+  T *data() { return m_pinned ? m_pinned : m_data.data(); }
+  const T *data() const { return m_pinned ? m_pinned : m_data.data(); }
+  T &operator[](size_t i) { return data()[i]; }
+  const T &operator[](size_t i) const { return data()[i]; }
+  void pin() {
+    if (m_pinned || count() == 0) return;
+    allocPinned();
+    std::copy(m_data.begin(), m_data.end(), m_pinned);
+    std::vector<T>().swap(m_data);
+  }
 
 private:
+  size_t count() const { return static_cast<size_t>(m_w) * m_h; }
+  void allocPinned() {
+    void *p = nullptr;
+    rthost::check(rt_pinned_alloc(count() * sizeof(T), &p), "Image2D::pin");
+    m_pinned = static_cast<T *>(p);
+  }
+  void release() {
+    if (m_pinned) rt_pinned_free(m_pinned);
+    m_pinned = nullptr;
+  }
   uint32_t m_w = 0, m_h = 0;
   std::vector<T> m_data;
+  T *m_pinned = nullptr;
 };
 
 struct FrameBuffer {  // raytracing.hpp:9-20
@@ -56,6 +82,12 @@ struct FrameBuffer {  // raytracing.hpp:9-20
   void clear() {
     color.clear(0);
     t.clear(std::numeric_limits<float>::infinity());
+  }
+  // B200 extension: page-locked storage.  Renderer::draw with frameIsCleared then lets the kernel store its tiles
+  // straight into the two images; without pin() the frame travels through pipelined copies.
+  void pin() {
+    color.pin();
+    t.pin();
   }
 };
 

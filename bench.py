@@ -458,7 +458,9 @@ def run_cuda(args):
                                                              "profiles/r1_e2e_ab.txt); the kernel's own stores are not affected"},
                "inout": {"value": px / inout_ms / 1e3, "ms_per_step": inout_ms, "h2d_bytes_per_step": 8 * px,
                          "d2h_bytes_per_step": 8 * px,
-                         "api": "rt_render_host, in/out framebuffer cleared on the host before each call (raytracing.cpp:17,90-94)"}}
+                         "api": "rt_render_host, in/out framebuffer cleared on the host before each call (raytracing.cpp:17,90-94); "
+                                "pinned buffers: the kernel bulk-loads each tile's previous colour + depth and stores "
+                                "the merged tile back"}}
         # the frame that came back must be the reference's frame (checked against the oracle, outside any timing)
 
     # ---- workload counters + roofline of the dominant (only) kernel

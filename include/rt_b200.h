@@ -166,10 +166,12 @@ int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *col
  * its own stopwatch, raytracing.cpp:97-101) and of the whole call incl. copies in *total_ms.  Any of prim,
  * device_ms, total_ms, counters may be NULL.
  * Page-locked framebuffer: when color and t_inout are pinned host memory (rt_pinned_alloc / rt_pinned_register below, or
- * any cudaHostAlloc / cudaHostRegister memory), rt_frame.clear = 1, the whole frame is rendered (band_count <= 1),
- * W % 8 == 0 and prim / counters are NULL, the kernel stores its tiles straight into the caller's buffers over PCIe
- * (128-byte bulk stores, no device framebuffer, no copy engine); *device_ms then equals *total_ms.  Pageable buffers
- * and every other combination go through the pipelined copies. */
+ * any cudaHostAlloc / cudaHostRegister memory), the whole frame is rendered (band_count <= 1), W % 8 == 0, prim /
+ * counters are NULL and no secondary rays are asked for, the kernel works on the caller's buffers directly over PCIe:
+ * with rt_frame.clear = 1 it stores its tiles as 128-byte bulk stores; with clear = 0 (the reference's in/out
+ * framebuffer) it first fetches each tile's previous colour and depth with bulk loads and stores the merged tile back.
+ * No device framebuffer, no copy engine; *device_ms then equals *total_ms.  Pageable buffers and every other
+ * combination go through the pipelined copies. */
 int rt_render_host(const rt_scene *scene, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
                    float *device_ms, float *total_ms, rt_counters *counters);
 

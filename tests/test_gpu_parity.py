@@ -342,6 +342,26 @@ for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "stanford-bun
     assert tms.value > 0.0
     assert util.same_bits(t.numpy().reshape(H, W), c["t"]), key
     assert np.array_equal(color.numpy().view(np.uint32).reshape(H, W), c["color_normal"]), key
+    # the reference's in/out contract (raytracing.cpp:90-94): left half cleared on the host, right half already holds a
+    # nearer surface that must survive
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+    cn, tn = color.numpy().view(np.uint32).reshape(H, W), t.numpy().reshape(H, W)
+    cn[:, :W // 2] = 0
+    tn[:, :W // 2] = np.inf
+    cn[:, W // 2:] = 7
+    tn[:, W // 2:] = 1e-3
+    L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(color.data_ptr()), C.c_void_p(t.data_ptr()), None,
+                                   C.byref(dms), C.byref(tms), None))
+    assert util.same_bits(tn[:, :W // 2], c["t"][:, :W // 2]), key
+    assert np.array_equal(cn[:, :W // 2], c["color_normal"][:, :W // 2]), key
+    if key.startswith("cube"):
+        # the 12-triangle cube goes through the brute-force kernel: triangle hits are not range-checked and
+        # there is no box test to cull them by, so the cube's pixels are overwritten and only the background survives
+        hitm = np.isfinite(c["t"][:, W // 2:])
+        assert util.same_bits(tn[:, W // 2:][hitm], c["t"][:, W // 2:][hitm]), key
+        assert np.all(cn[:, W // 2:][~hitm] == 7) and np.all(tn[:, W // 2:][~hitm] == np.float32(1e-3)), key
+    else:
+        assert np.all(cn[:, W // 2:] == 7) and np.all(tn[:, W // 2:] == np.float32(1e-3)), key
 print("zero-copy ok")
 """
     env = dict(os.environ, RT_HOST_ZEROCOPY=mode)

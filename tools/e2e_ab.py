@@ -37,7 +37,14 @@ for scene_name, W, H in cases:
     for _ in range(10):
         color.fill_(0x5A5A5A5A); t.fill_(0.25)
         t0 = time.perf_counter(); call(); td.append((time.perf_counter() - t0) * 1e3)
-    print(f"mode {mode} {scene_name:15s} {W}x{H}  mean {np.mean(ts):.4f} ms  min {np.min(ts):.4f}  after-cpu-rewrite {np.mean(td):.4f}  "
+    f = rt.make_frame(c["rayPos"], c["viewInv"], pinv, W, H)   # in/out contract: the caller clears on the host
+    ti = []
+    for _ in range(12):
+        color.zero_(); t.fill_(float("inf"))
+        t0 = time.perf_counter(); call(); ti.append((time.perf_counter() - t0) * 1e3)
+    hit2 = int((t.numpy() < 1e30).sum())
+    assert hit2 == hit, (hit, hit2)
+    print(f"mode {mode} {scene_name:15s} {W}x{H}  mean {np.mean(ts):.4f} ms  min {np.min(ts):.4f}  after-cpu-rewrite {np.mean(td):.4f}  inout {np.mean(ti[2:]):.4f}  "
           f"floor56 {W*H*8/56e9*1e3:.4f}  hits {hit}  csum {int(color.numpy().view(np.uint32).astype(np.uint64).sum())}", flush=True)
 """
 

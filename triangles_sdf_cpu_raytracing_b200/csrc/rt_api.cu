@@ -422,11 +422,13 @@ const int g_env_tile_block = env_int("RT_TILE_BLOCK");
 const int g_env_host_chunks = env_int("RT_HOST_CHUNKS");
 const int g_env_stage = std::getenv("RT_STAGE_STORES") ? env_int("RT_STAGE_STORES") : -1;  // -1: peer framebuffers only
 // RT_HOST_ZEROCOPY: rt_render_host with a pinned host framebuffer; 0 = copy pipeline, 1 = kernel stores straight into the
-// host buffers, 2 = the same through the staged 128-byte bulk stores.  Unset = 2, by measurement (profiles/r1_e2e_ab.txt,
+// host buffers, 2 = the same through the staged 128-byte bulk stores, 3 = 2 but the in/out contract (clear = 0) keeps
+// the copies.  Unset = 2, by measurement (profiles/r1_e2e_ab.txt,
 // B200, PCIe Gen5): 1080p 0.397 -> 0.346 ms, and 0.58 -> 0.35 ms when the CPU has just rewritten the buffers (the
 // reference clears on the host before every draw: dirty cache lines slow the copy engine's writes, not these);
-// 4K 1.235 -> 1.295 ms untouched, 1.60 -> 1.31 ms rewritten.  Plain 32-byte stores (1) are 1.7x slower than the copies;
-// 256-byte bulk stores measured the same as 128-byte ones.
+// 4K 1.235 -> 1.295 ms untouched, 1.60 -> 1.31 ms rewritten; sdf_6 octree 4K 1.79 -> 1.32 ms; in/out contract at 1080p
+// 0.913 -> 0.458 ms.  Plain 32-byte stores (1) are 1.7x slower than the copies; 256-byte bulk stores measured the same
+// as 128-byte ones.
 constexpr int HOST_ZEROCOPY_DEFAULT = 2;
 const int g_env_zero_copy = std::getenv("RT_HOST_ZEROCOPY") ? env_int("RT_HOST_ZEROCOPY") : HOST_ZEROCOPY_DEFAULT;
 const int g_env_oct_refill = env_int("RT_OCT_REFILL");
@@ -459,15 +461,18 @@ int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color,
   // 128-byte TMA bulk writes.  Needs the fused clear (whole tiles are written) and 32-byte-multiple rows.
   a.stage_stores = 0;
   int sched = resolve_sched(scene);
-  if (fd.clear && !prim && !counters_dev && fd.W % 8u == 0u && (force_stage >= 0 ? force_stage == 1 : g_env_stage != 0)) {
-    bool peer = g_env_stage == 1 || force_stage == 1;
+  // (force_stage, from rt_render_host with a pinned host framebuffer: 0 = plain stores, 1 = staged with the fused clear,
+  // 2 = staged in/out, the tile's previous contents fetched by bulk loads)
+  if ((fd.clear || force_stage == 2) && !prim && !counters_dev && fd.W % 8u == 0u &&
+      (force_stage >= 0 ? force_stage >= 1 : g_env_stage != 0)) {
+    bool peer = g_env_stage == 1 || force_stage >= 1;
     // measured (profiles/r1_multi/TABLE.txt): pays when rank 0's inbound NVLink is saturated, i.e. on 8 GPUs at 4K
     // (grid 0.139 -> 0.096 ms, bunny 0.147 -> 0.125 ms); not at 1080p (0.051 -> 0.053 ms), mixed on 4 GPUs (grid 0.131 ->
     // 0.124, bunny 0.139 -> 0.165 ms) and slower on 2 (grid 0.196 -> 0.214 ms): the 32 x 4 block with its barrier is a
     // slower kernel than the 16 x 8 one
     if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
       peer = is_peer_pointer(color) && is_peer_pointer(t_out);
-    a.stage_stores = peer ? 1 : 0;
+    a.stage_stores = peer ? (force_stage == 2 ? 2 : 1) : 0;
     if (peer && force_stage < 0) g_staged_launches.fetch_add(1);  // counts the multi-GPU path only
     // the staged stores live in the tiles kernel: for a peer framebuffer the octree's default (persistent, ~1 % faster
     // on one GPU) gives way to it
@@ -568,13 +573,17 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   const int sched_now = g_sched.load();
   const bool staged_ok = !secondary && !(s->kind == RT_SCENE_MESH && s->dev.mesh.brute) &&
                          (sched_now == RT_SCHED_AUTO || sched_now == RT_SCHED_TILES);
-  if (g_env_zero_copy != 0 && (g_env_zero_copy == 1 || staged_ok) && fd.band_count <= 1 && fd.clear && !prim &&
-      !counters && fd.W % 8u == 0u) {
+  // The in/out contract (clear = 0) takes the same route in mode 2: the kernel fetches each tile's previous colour and
+  // depth from the host buffers with bulk loads and sends the merged tile back.
+  const bool inout = !fd.clear;
+  if (g_env_zero_copy != 0 && (inout ? (g_env_zero_copy == 2 && staged_ok) : (g_env_zero_copy == 1 || staged_ok)) &&
+      fd.band_count <= 1 && !prim && !counters && fd.W % 8u == 0u) {
     uint32_t *dc = static_cast<uint32_t *>(mapped_host_pointer(color));
     float *dt = static_cast<float *>(mapped_host_pointer(t_inout));
     if (dc && dt) {
       RT_CUDA(cudaEventRecord(s->ev[0], st));
-      rc = render_on_stream(s, fd, dc, nullptr, dt, nullptr, nullptr, st, g_env_zero_copy >= 2 ? 1 : 0);
+      rc = render_on_stream(s, fd, dc, inout ? dt : nullptr, dt, nullptr, nullptr, st,
+                            inout ? 2 : (g_env_zero_copy >= 2 ? 1 : 0));
       if (rc) return rc;
       RT_CUDA(cudaEventRecord(s->ev[3], st));
       RT_CUDA(cudaStreamSynchronize(st));

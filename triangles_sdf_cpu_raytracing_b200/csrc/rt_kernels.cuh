@@ -264,38 +264,85 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
   if (COUNT) flush_counters(cnt, a.counters);
 }
 
-// ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (multi-GPU: peer framebuffer) ----------
-// When the framebuffer lives on ANOTHER GPU (rank 0's, mapped over CUDA IPC) the plain kernel's stores cross NVLink as
-// 32-byte pieces (one 8-pixel tile row per warp).  Here a block owns 32 x 4 pixels: every thread parks its pixel in
-// shared memory, and after one barrier four threads issue the block's eight 128-byte row segments (colour + depth) as
-// bulk asynchronous stores (cp.async.bulk shared -> global, SASS UBLKCP): full 128-byte NVLink writes, no per-thread
-// store instructions.  Needs the fused clear (every pixel of the tile is written) and W % 8 == 0; primary rays only.
-template <int KIND>
+// ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (peer or pinned-host framebuffer) --------
+// When the framebuffer lives on ANOTHER GPU (rank 0's, mapped over CUDA IPC) or in page-locked HOST memory
+// (rt_render_host), the plain kernel's stores cross NVLink / PCIe as 32-byte pieces (one 8-pixel tile row per warp).
+// Here a block owns 32 x 4 pixels: every thread parks its pixel in shared memory, and after one barrier four threads
+// issue the block's eight 128-byte row segments (colour + depth) as bulk asynchronous stores (cp.async.bulk shared ->
+// global, SASS UBLKCP): full 128-byte writes, no per-thread store instructions.  W % 8 == 0; primary rays only.
+//   INOUT = false: fused clear, every pixel of the tile is produced here.
+//   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous colour and depth are
+//                  first fetched into the same shared-memory rows by bulk loads completing on an mbarrier; a pixel is
+//                  replaced only by a nearer hit, and the whole tile goes back.
+template <int KIND, bool INOUT>
 __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
   __shared__ __align__(128) uint32_t sColor[4][32];
   __shared__ __align__(128) float sDepth[4][32];
+  __shared__ __align__(8) unsigned long long mbar;
   const FrameDev &f = a.frame;
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   const uint32_t x0 = blockIdx.x * 32u, v0 = centre_out(blockIdx.y, gridDim.y) * 4u;
   const uint32_t lx = warp * TILE_W + (lane & 7u), ly = lane >> 3;
   const uint32_t x = x0 + lx, v = v0 + ly;
+  const uint32_t rowBytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
+  if (INOUT) {
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t rows = 0;
+#pragma unroll
+      for (uint32_t r = 0; r < 4u; ++r)
+        if (v0 + r < f.rows_here && band_row(f, v0 + r) < f.H) ++rows;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rows * 2u * rowBytes)
+                   : "memory");
+#pragma unroll
+      for (uint32_t r = 0; r < 4u; ++r) {
+        if (!(v0 + r < f.rows_here)) continue;
+        const uint32_t row = band_row(f, v0 + r);
+        if (!(row < f.H)) continue;
+        const size_t px = (size_t)row * f.W + x0;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(&sColor[r][0])),
+                     "l"(a.color + px), "r"(rowBytes), "r"(bar)
+                     : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(&sDepth[r][0])),
+                     "l"(a.t_in + px), "r"(rowBytes), "r"(bar)
+                     : "memory");
+      }
+    }
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(0)
+          : "memory");
+    }
+  }
   Counters cnt = {};
   if (x < f.W && v < f.rows_here) {
     const uint32_t row = band_row(f, v);
     if (row < f.H) {
       const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
       const V3 d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
+      const float tPrev = INOUT ? sDepth[ly][lx] : __int_as_float(0x7f800000);
       C4 col;
       float tNew = __int_as_float(0x7f800000);
-      uint32_t prim, packed = 0u;
-      if (intersection_color<KIND, false, false>(a.scene, f, nullptr, o, d, __int_as_float(0x7f800000), col, tNew, prim,
-                                                 cnt) &&
-          !isinf(tNew))
-        packed = color_pack_rgba(col);
-      else
-        tNew = __int_as_float(0x7f800000);
-      sColor[ly][lx] = packed;
-      sDepth[ly][lx] = tNew;
+      uint32_t prim;
+      if (intersection_color<KIND, false, false>(a.scene, f, nullptr, o, d, tPrev, col, tNew, prim, cnt) && !isinf(tNew)) {
+        sColor[ly][lx] = color_pack_rgba(col);
+        sDepth[ly][lx] = tNew;
+      } else if (!INOUT) {  // fused FrameBuffer::clear (raytracing.hpp:16-19)
+        sColor[ly][lx] = 0u;
+        sDepth[ly][lx] = __int_as_float(0x7f800000);
+      }
     }
   }
   __syncthreads();
@@ -303,14 +350,13 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
     const uint32_t vr = v0 + threadIdx.x;
     const uint32_t row = vr < f.rows_here ? band_row(f, vr) : f.H;
     if (row < f.H && x0 < f.W) {
-      const uint32_t bytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
       const size_t px = (size_t)row * f.W + x0;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> async proxy
       asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.color + px),
-                   "r"((uint32_t)__cvta_generic_to_shared(&sColor[threadIdx.x][0])), "r"(bytes)
+                   "r"((uint32_t)__cvta_generic_to_shared(&sColor[threadIdx.x][0])), "r"(rowBytes)
                    : "memory");
       asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.t_out + px),
-                   "r"((uint32_t)__cvta_generic_to_shared(&sDepth[threadIdx.x][0])), "r"(bytes)
+                   "r"((uint32_t)__cvta_generic_to_shared(&sDepth[threadIdx.x][0])), "r"(rowBytes)
                    : "memory");
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -530,7 +576,8 @@ static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count,
     if (KIND == KIND_BRUTE) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
     if (!COUNT && !SECONDARY && a.stage_stores) {
       dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 3u) / 4u);
-      render_tiles_staged_kernel<KIND><<<grid, 128, 0, st>>>(a);
+      if (a.stage_stores == 2) render_tiles_staged_kernel<KIND, true><<<grid, 128, 0, st>>>(a);
+      else render_tiles_staged_kernel<KIND, false><<<grid, 128, 0, st>>>(a);
       return cudaGetLastError();
     }
     if (!COUNT && !SECONDARY) {

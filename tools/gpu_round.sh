@@ -28,4 +28,7 @@ b bunny_s2_4k_lbvh_gpu --scene bunny_s2_4k --steps 50 --warmup 5 --mesh-accel lb
 b bunny_s2_orbit64_4k --scene bunny_s2_orbit64_4k --steps 64 --warmup 5
 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err
 python bench.py --impl reference --scene bunny_s2_orbit64_4k --steps 4 --warmup 1 > gpurun_out/bench_reference_orbit.json 2> gpurun_out/bench_reference_orbit.err
+# host-call transfer modes side by side (copies / stores with in-out through copies / stores both ways)
+E2E_SCENES=example_grid:1920x1080,example_grid:3840x2160,sdf_6:1920x1080,sdf_6:3840x2160,stanford-bunny:1920x1080,stanford-bunny:3840x2160 \
+  python tools/e2e_ab.py 0,3,2 > gpurun_out/e2e_ab.log 2>&1
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; python tools/bench_table.py

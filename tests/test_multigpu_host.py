@@ -69,3 +69,27 @@ def _worker(rank, world, port, H, W, band):
 
 def test_two_rank_gloo_tile_gather():
     mp.spawn(_worker, args=(2, _free_port(), 45, 16, 8), nprocs=2, join=True)
+
+
+def test_partition_matches_the_library_arithmetic_property():
+    """Property test (hypothesis): for any frame height / band size / rank count, the rows a rank owns according to the
+    host module are exactly the rows the library's launch arithmetic visits: make_frame sizes the launch to
+    rows_here = my_bands * band_rows virtual rows (csrc/rt_api.cu) and the kernels map virtual row v to frame row
+    (v / band_rows * band_count + band_index) * band_rows + v % band_rows, dropping rows >= H (csrc/rt_kernels.cuh)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=300, deadline=None)
+    @given(st.integers(1, 4400), st.integers(1, 64), st.integers(2, 8))
+    def check(H, band, count):
+        seen = np.zeros(H, np.int32)
+        n_bands = (H + band - 1) // band
+        for i in range(count):
+            mine = (n_bands - i + count - 1) // count if n_bands > i else 0
+            v = np.arange(mine * band)
+            rows = (v // band * count + i) * band + v % band
+            rows = rows[rows < H]
+            assert np.array_equal(rows, M.band_rows_of(H, band, count, i))
+            seen[rows] += 1
+        assert np.all(seen == 1)
+
+    check()

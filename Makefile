@@ -24,11 +24,11 @@ $(OBJ)/rt_host.o: $(HOST)/rt_host.cpp $(HOST)/scenes.hpp $(HOST)/raytracing.hpp 
 $(EXAMPLE): $(HOST)/example_frame_loop.cpp $(HOST)/scenes.hpp $(HOST)/raytracing.hpp $(HOST)/camera.hpp $(HOST)/rt_math.hpp $(OUT)
 	g++ -std=c++17 -O2 -ffp-contract=off -Wall -Wextra -o $@ $< -L$(PKG) -lrt_b200 -Wl,-rpath,'$$ORIGIN/..'
 
-$(OBJ)/rt_kernels_exact.o: $(CSRC)/rt_kernels_exact.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
+$(OBJ)/rt_kernels_exact.o: $(CSRC)/rt_kernels_exact.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_shade.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
 
-$(OBJ)/rt_kernels_fast.o: $(CSRC)/rt_kernels_fast.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
+$(OBJ)/rt_kernels_fast.o: $(CSRC)/rt_kernels_fast.cu $(CSRC)/rt_kernels.cuh $(CSRC)/rt_shade.cuh $(CSRC)/rt_device.cuh $(CSRC)/rt_scene.h include/rt_b200.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -fmad=true -c $< -o $@
 

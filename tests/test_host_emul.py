@@ -1,0 +1,244 @@
+"""CPU: the product's per-ray CUDA source (csrc/rt_device.cuh + csrc/rt_shade.cuh) compiled as plain C++
+(tests/host_emul/) against the golden frames of the reference and against the plain-C oracle on seeded cameras.
+
+The GPU parity tests check the kernels on a few dozen frames; this file runs the same source text on the CPU over
+hundreds of cameras (eyes inside the [-1,1]^3 box and inside meshes included), every shading mode, secondary rays, the
+ground plane and the in/out depth buffer, bit for bit.  It covers the arithmetic and control flow of the per-ray code;
+what only exists on the device (tiles, bands, shared-memory staging, TMA stores, warp votes) is the GPU tests' job."""
+import numpy as np
+import pytest
+
+import triangles_sdf_cpu_raytracing_b200 as rt
+from oracle import port_oracle as P
+from tests import util
+from tests import host_emul as E
+
+G = util.Golden()
+# rt_counters name -> the oracle's name
+COUNTERS = {"grid": {"rays": "rays", "hits": "hits", "grid_samples": "gridSdf"},
+            "octree": {"rays": "rays", "hits": "hits", "oct_inner": "octInner", "oct_leaf": "octLeaf",
+                       "oct_leaf_samples": "octLeafSdf"}}
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    if E.cuda_include() is None:
+        pytest.skip("no CUDA headers on this machine (float4 / make_float4 come from cuda_runtime.h)")
+    E.build()
+
+
+def emul_scene(name, **kw):
+    a = G.scene_arrays(name)
+    if "values" in a:
+        return E.EmulScene.grid(a["values"]), "grid"
+    if "nodes36" in a:
+        return E.EmulScene.octree(a["nodes36"]), "octree"
+    return E.EmulScene.mesh(a["vpos4"], a["indices"], **kw), "mesh"
+
+
+def seeded_cameras(n, seed, radii=(0.2, 0.35, 0.9, 1.0, 1.6, 2.5, 4.0)):
+    """Eyes on spheres of the given radii (< 1.74: inside the bounding sphere of the [-1,1]^3 box), off-centre targets,
+    locked / free up vector, mouse rotations: (rayPos, viewInv) through the host mirror of Camera (camera.cpp)."""
+    rng = np.random.default_rng(seed)
+    for k in range(n):
+        v = rng.normal(size=3)
+        eye = float(rng.choice(radii)) * v / np.linalg.norm(v)
+        target = rng.uniform(-0.3, 0.3, size=3)
+        pos, _view, vinv = rt.host_camera(eye=tuple(float(x) for x in eye), target=tuple(float(x) for x in target),
+                                          lock_up=bool(k % 2), n_rotate=int(rng.integers(0, 4)),
+                                          dx=float(rng.uniform(-80, 80)), dy=float(rng.uniform(-40, 40)))
+        yield k, pos, vinv
+
+
+@pytest.mark.parametrize("key", G.cases)
+def test_device_source_on_cpu_reproduces_the_golden_frames(key):
+    c = G.case(key)
+    s, kind = emul_scene(c["scene"])
+    W, H = c["W"], c["H"]
+    for mode, name in ((rt.SHADE_NORMAL, "color_normal"), (rt.SHADE_LAMBERT, "color_lambert"), (rt.SHADE_COLOR, "color_color")):
+        col, t, prim, _ = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=mode))
+        assert util.same_bits(t, c["t"]), f"{key}: depth differs"
+        if kind == "mesh":  # exact-t ties between two triangles: the winner depends on the tree
+            assert (col != c[name]).sum() <= max(2, 1e-3 * W * H), f"{key}: {name} differs beyond tie pixels"
+        else:
+            assert np.array_equal(col, c[name]), f"{key}: {name} differs"
+    if "color_full" in c and c["color_full"] is not None and kind != "mesh":
+        f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=rt.SHADE_LAMBERT, shadows=True,
+                          reflections=True, plane_y=-1.0)
+        col, t, _, _ = s.render(f)
+        assert util.same_bits(t, c["t_full"]) and np.array_equal(col, c["color_full"]), f"{key}: plane + secondary rays"
+
+
+@pytest.mark.parametrize("name,n_cams", (("example_grid", 150), ("sdf_6", 150), ("sdf_5", 100)))
+def test_device_source_on_cpu_vs_oracle_seeded_cameras_sdf(name, n_cams):
+    """SDF scenes are tree-free: colour, depth AND the visit counters must equal the oracle's on every camera."""
+    s, kind = emul_scene(name)
+    ps = util.port_scene(G, name)
+    W, H = 72, 48
+    pinv = rt.host_projection(W, H)[1]
+    for k, pos, vinv in seeded_cameras(n_cams, seed=1000 + len(name)):
+        mode = (rt.SHADE_NORMAL, rt.SHADE_LAMBERT, rt.SHADE_COLOR)[k % 3]
+        plane = (k % 5 == 0)
+        f = rt.make_frame(pos, vinv, pinv, W, H, mode=mode, shadows=plane, reflections=plane,
+                          plane_y=-1.0 if plane else None)
+        col, t, _, cnt = s.render(f)
+        sc = ps.with_plane(-1.0) if plane else ps
+        pc, pt, _, pcnt = sc.render(pos, vinv, pinv, W, H, mode=mode, shadows=plane, reflections=plane, want_counters=True)
+        assert util.same_bits(t, pt), f"{name} camera {k}: depth differs on {(util.bits(t) != util.bits(pt)).sum()} pixels"
+        assert np.array_equal(col, pc), f"{name} camera {k}: colour differs on {(col != pc).sum()} pixels"
+        for cn, pn in COUNTERS[kind].items():
+            assert cnt[cn] == pcnt[pn], f"{name} camera {k}: counter {cn} {cnt[cn]} != {pcnt[pn]}"
+
+
+@pytest.mark.parametrize("name", ("example_grid", "sdf_6"))
+def test_device_source_on_cpu_in_out_depth_buffer(name):
+    """raytracing.cpp:90-94: a pixel is replaced only by a nearer hit; the previous depth also bounds the march."""
+    s, _ = emul_scene(name)
+    ps = util.port_scene(G, name)
+    W, H = 64, 40
+    pinv = rt.host_projection(W, H)[1]
+    rng = np.random.default_rng(5)
+    for k, pos, vinv in seeded_cameras(12, seed=77, radii=(1.6, 2.5)):
+        t0 = rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
+        c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
+        col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
+        pc, pt, _, _ = ps.render(pos, vinv, pinv, W, H, color=c0, t=t0)
+        assert util.same_bits(t, pt) and np.array_equal(col, pc), f"{name} camera {k}"
+        assert (t != t0).any() and (t == t0).any()  # some pixels replaced, some kept
+
+
+@pytest.mark.parametrize("name,n_cams", (("cube", 60), ("stanford-bunny", 12), ("spot", 12), ("as1-oc-214", 12)))
+def test_device_source_on_cpu_vs_oracle_seeded_cameras_mesh_outside(name, n_cams):
+    """Our own BVH8 (and the brute-force path for the cube) against the oracle's every-triangle loop from outside the
+    mesh, where the closest hit does not depend on the tree: depth bit for bit, colour bar exact-t ties."""
+    try:
+        s, _ = emul_scene(name)
+    except Exception:
+        pytest.skip(f"{name} is not among the fixtures")
+    ps = util.port_scene(G, name)
+    W, H = 64, 40
+    pinv = rt.host_projection(W, H)[1]
+    ties = 0
+    for k, pos, vinv in seeded_cameras(n_cams, seed=31 + len(name), radii=(1.8, 2.5, 4.0)):
+        col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H))
+        pc, pt, _, _ = ps.render(pos, vinv, pinv, W, H)
+        assert util.same_bits(t, pt), f"{name} camera {k}: depth differs on {(util.bits(t) != util.bits(pt)).sum()} pixels"
+        ties += int((col != pc).sum())
+    assert ties <= 2e-3 * n_cams * W * H, f"{name}: {ties} colour mismatches"
+
+
+def test_brute_force_and_bvh_paths_agree_on_the_cube():
+    a = G.scene_arrays("cube")
+    sb = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=True)
+    st = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=False)
+    W, H = 64, 40
+    pinv = rt.host_projection(W, H)[1]
+    for k, pos, vinv in seeded_cameras(40, seed=9, radii=(1.8, 2.5, 4.0)):
+        f = rt.make_frame(pos, vinv, pinv, W, H)
+        cb, tb, _, _ = sb.render(f)
+        ct, tt, _, _ = st.render(f)
+        assert util.same_bits(tb, tt), f"camera {k}"
+        assert (cb != ct).sum() <= 0.01 * W * H  # shared edges of the cube's faces
+
+
+@pytest.mark.ref
+@pytest.mark.parametrize("name,n_cams", (("cube", 40), ("stanford-bunny", 16)))
+def test_device_source_on_cpu_reference_built_tree_inside_and_outside(name, n_cams):
+    """rt_scene_create_mesh_bvh8's path (literal slab test + sort8 order over the tree the reference built) against the
+    compiled reference itself, eyes inside the mesh included: there unchecked triangle hits make the answer
+    tree-dependent, and with the same tree it must still be the reference's, bit for bit, prim ids included."""
+    from oracle import ref_oracle as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    a = G.scene_arrays(name)
+    ro = R.RefOracle()
+    ref = ro.mesh(a["vpos4"], a["indices"])
+    m = ref.export_mesh()
+    s = E.EmulScene.mesh_refbvh(m["vpos4"], m["indices"], m["nodes"], m["prim_of_permuted"])
+    W, H = 56, 40
+    pinv = ro.projection(W, H)[1]
+    rng = np.random.default_rng(123)
+    for k in range(n_cams):
+        v = rng.normal(size=3)
+        eye = tuple(float(x) for x in float(rng.choice([0.2, 0.5, 0.9, 1.6, 2.5])) * v / np.linalg.norm(v))
+        cam = R.CamSpec(eye=eye, target=tuple(float(x) for x in rng.uniform(-0.3, 0.3, size=3)), lock_up=bool(k % 2),
+                        n_rotate=int(rng.integers(0, 4)), dx=float(rng.uniform(-80, 80)), dy=float(rng.uniform(-40, 40)))
+        pos, _view, vinv = ro.camera(cam)
+        for mode_ref, mode in ((R.MODE_NORMAL, rt.SHADE_NORMAL), (R.MODE_LAMBERT, rt.SHADE_LAMBERT)):
+            want_c, want_t, _ = ref.render(cam, W, H, proj_inv=pinv, mode=mode_ref)
+            col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H, mode=mode))
+            assert util.same_bits(t, want_t), f"{name} camera {k} {cam}: depth differs"
+            assert np.array_equal(col, want_c), f"{name} camera {k} {cam}: colour differs"
+
+
+def test_brick_layout_is_the_linear_layout():
+    """RT_GRID_BRICKS only changes where a sample lives: frames and sample counts are those of the linear layout."""
+    a = G.scene_arrays("example_grid")
+    lin, bri = E.EmulScene.grid(a["values"]), E.EmulScene.grid(a["values"], bricks=True)
+    W, H = 72, 48
+    pinv = rt.host_projection(W, H)[1]
+    for k, pos, vinv in seeded_cameras(60, seed=4):
+        f = rt.make_frame(pos, vinv, pinv, W, H, mode=rt.SHADE_LAMBERT)
+        c0, t0, _, n0 = lin.render(f)
+        c1, t1, _, n1 = bri.render(f)
+        assert util.same_bits(t0, t1) and np.array_equal(c0, c1) and n0 == n1, f"camera {k}"
+    # a grid whose size is not a multiple of 8 in any axis: partial bricks
+    v = np.ascontiguousarray(a["values"][:61, 3:62, :59])
+    lin, bri = E.EmulScene.grid(v), E.EmulScene.grid(v, bricks=True)
+    for k, pos, vinv in seeded_cameras(20, seed=5):
+        f = rt.make_frame(pos, vinv, pinv, W, H)
+        c0, t0, _, _ = lin.render(f)
+        c1, t1, _, _ = bri.render(f)
+        assert util.same_bits(t0, t1) and np.array_equal(c0, c1), f"partial bricks, camera {k}"
+
+
+def _ray_batch(seed, n_random=1500):
+    """Exactly axis-parallel rays (a zero direction component makes 1/d infinite and 0 * inf = NaN in the slab tests,
+    SURVEY T11) from origins on cell boundaries, box faces and box corners, plus random rays from inside and outside."""
+    rng = np.random.default_rng(seed)
+    o, d = [], []
+    axes = np.eye(3, dtype=np.float32)
+    lattice = np.array([-1.0, -0.5, -1.0 / 32, 0.0, 1.0 / 64, 0.25, 1.0], np.float32)
+    for ax in range(3):
+        for sgn in (1.0, -1.0):
+            for u in lattice:
+                for v in lattice:
+                    p = np.zeros(3, np.float32)
+                    p[ax] = -2.5 * sgn
+                    p[(ax + 1) % 3], p[(ax + 2) % 3] = u, v
+                    o.append(p)
+                    d.append(axes[ax] * np.float32(sgn))
+                    q = p.copy()
+                    q[ax] = np.float32(0.125 * sgn)  # starting inside the box
+                    o.append(q)
+                    d.append(axes[ax] * np.float32(sgn))
+    # two zero components / one zero component
+    for _ in range(200):
+        p = rng.uniform(-1.5, 1.5, 3).astype(np.float32)
+        v = rng.normal(size=3).astype(np.float32)
+        v[rng.integers(0, 3)] = 0.0
+        o.append(p)
+        d.append(v / np.linalg.norm(v))
+    for _ in range(n_random):
+        p = (rng.uniform(-1, 1, 3) * rng.choice([0.5, 1.0, 3.0])).astype(np.float32)
+        v = rng.normal(size=3).astype(np.float32)
+        o.append(p)
+        d.append((v / np.linalg.norm(v)).astype(np.float32))
+    return np.asarray(o, np.float32), np.asarray(d, np.float32)
+
+
+@pytest.mark.parametrize("name", ("example_grid", "sdf_6", "sdf_5", "cube"))
+def test_device_source_on_cpu_single_rays_vs_oracle(name):
+    """IScene::intersect (rays_kernel's body): hit flag, t and normal bit for bit, axis-parallel rays included."""
+    s, kind = emul_scene(name)
+    ps = util.port_scene(G, name)
+    o, d = _ray_batch(seed=len(name))
+    for t_near, t_far, plane in ((0.01, 100.0, None), (0.3, 2.2, None), (0.01, 100.0, -1.0)):
+        hit, t, nrm, _ = s.intersect(o, d, t_near, t_far, plane_y=plane)
+        sc = ps.with_plane(plane) if plane is not None else ps
+        for i in range(o.shape[0]):
+            h, pt, pn, _ = sc.intersect(o[i], d[i], t_near, t_far)
+            assert bool(hit[i]) == h, f"{name} ray {i} o={o[i]} d={d[i]}: hit {hit[i]} vs {h}"
+            if h:
+                assert util.same_bits(t[i], pt), f"{name} ray {i} o={o[i]} d={d[i]}: t {t[i]} vs {pt}"
+                assert util.same_bits(nrm[i], pn), f"{name} ray {i} o={o[i]} d={d[i]}: normal {nrm[i]} vs {pn}"

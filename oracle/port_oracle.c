@@ -453,9 +453,14 @@ static BvhHit bvh_node(const PortScene *s, uint32_t index, v3 o, v3 d, float tNe
 }
 
 /* No BVH given: every triangle in index order, first closest wins (the loop ray_pack.ispc:167-202 describes,
- * with the leaf acceptance rule of triangles_raytracing.cpp:324-331: no t-range test). Tree-independent truth
- * for meshes whose reference-built BVH is not at hand (the GPU box). nIdx is passed in nBvhNodes' place. */
-static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, PortCounters *cnt) {
+ * with the leaf acceptance rule of triangles_raytracing.cpp:324-331: no t-range test on the triangle itself).
+ * Tree-independent truth for meshes whose reference-built BVH is not at hand (the GPU box). nIdx is passed in
+ * nBvhNodes' place.  The one thing a tree adds to the answer is box culling against [tNear, tFar]
+ * (triangles_raytracing.cpp:266-297): a hit beyond tFar (the depth already in the framebuffer) lies in leaf boxes that
+ * start beyond tFar and is never reached, while hits before tNear or behind the origin are (their boxes straddle the
+ * origin).  `th <= tFar` restates that; checked against the compiled reference on the cube, from outside and inside,
+ * cleared and pre-filled depth buffers (tests/test_host_emul.py, tests/test_oracle_port.py). */
+static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, float tFar, PortCounters *cnt) {
   BvhHit result = {0, INFINITY, 0};
   uint32_t nTri = s->bvhNodeBytes; /* triangle count when bvhNodes == NULL */
   for (uint32_t k = 0; k < nTri; ++k) {
@@ -464,7 +469,7 @@ static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, PortCounters *cnt) {
     v3 v1 = mesh_vertex(s, s->indices[3 * k + 1]);
     v3 v2 = mesh_vertex(s, s->indices[3 * k + 2]);
     float th;
-    if (tri_lane(o, d, v0, v1, v2, &th) && (!result.hitten || result.t > th)) {
+    if (tri_lane(o, d, v0, v1, v2, &th) && th <= tFar && (!result.hitten || result.t > th)) {
       result.hitten = 1;
       result.t = th;
       result.tri = k;
@@ -475,7 +480,7 @@ static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, PortCounters *cnt) {
 
 static Hit mesh_intersect(const PortScene *s, v3 o, v3 d, float tNear, float tFar, PortCounters *cnt) {
   Hit r = hit_none();
-  BvhHit b = s->bvhNodes ? bvh_node(s, 0, o, d, tNear, tFar, cnt) : mesh_brute(s, o, d, cnt);
+  BvhHit b = s->bvhNodes ? bvh_node(s, 0, o, d, tNear, tFar, cnt) : mesh_brute(s, o, d, tFar, cnt);
   if (!b.hitten) return r;
   r.hitten = 1;
   r.t = b.t;

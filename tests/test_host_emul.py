@@ -242,3 +242,44 @@ def test_device_source_on_cpu_single_rays_vs_oracle(name):
             if h:
                 assert util.same_bits(t[i], pt), f"{name} ray {i} o={o[i]} d={d[i]}: t {t[i]} vs {pt}"
                 assert util.same_bits(nrm[i], pn), f"{name} ray {i} o={o[i]} d={d[i]}: normal {nrm[i]} vs {pn}"
+
+
+@pytest.mark.ref
+def test_brute_force_path_matches_the_reference_with_a_prefilled_depth_buffer():
+    """The <= 32-triangle kernel has no tree, the reference culls by its leaf boxes: `t <= tFar` per triangle reproduces
+    it on the cube (BASELINE configs[0]) from outside and inside, on cleared and pre-filled depth buffers."""
+    from oracle import ref_oracle as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    a = G.scene_arrays("cube")
+    ro = R.RefOracle()
+    ref = ro.mesh(a["vpos4"], a["indices"])
+    s = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=True)
+    W, H = 64, 40
+    pinv = ro.projection(W, H)[1]
+    rng = np.random.default_rng(3)
+    for radii in ((1.8, 2.5, 4.0), (0.2, 0.5, 0.9)):
+        for prefill in (True, False):
+            for k in range(30):
+                v = rng.normal(size=3)
+                eye = tuple(float(x) for x in float(rng.choice(radii)) * v / np.linalg.norm(v))
+                cam = R.CamSpec(eye=eye, target=tuple(float(x) for x in rng.uniform(-0.3, 0.3, size=3)), lock_up=bool(k % 2))
+                pos, _view, vinv = ro.camera(cam)
+                t0 = (rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
+                      if prefill else np.full((H, W), np.inf, np.float32))
+                c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
+                want_c, want_t, _ = ref.render(cam, W, H, proj_inv=pinv, color=c0, t=t0)
+                col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
+                assert util.same_bits(t, want_t), f"radii {radii} prefill {prefill} camera {k}: depth differs"
+                assert (col != want_c).sum() <= 0.01 * W * H  # exact-t ties on the cube's shared edges
+
+
+def test_brute_force_path_golden_prefilled_frames():
+    a = G.scene_arrays("cube")
+    s = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=True)
+    for key in [c for c in G.cases if c.startswith("cube|")]:
+        c = G.case(key)
+        t0 = np.full((c["H"], c["W"]), 2.2, np.float32)
+        c0 = np.full((c["H"], c["W"]), 0x11223344, np.uint32)
+        col, t, _, _ = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"]), color=c0, t=t0)
+        assert util.same_bits(t, c["t_prefilled"]) and np.array_equal(col, c["color_prefilled"]), key

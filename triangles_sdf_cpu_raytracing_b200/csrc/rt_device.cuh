@@ -796,14 +796,19 @@ done:
 
 // Every triangle against the ray, triangles staged in shared memory by the kernel (smem = n_tris x 3 float4).
 template <bool COUNT>
-__device__ __forceinline__ Hit brute_intersect(const float4 *smemTris, uint32_t nTris, V3 o, V3 d, Counters &cnt) {
+__device__ __forceinline__ Hit brute_intersect(const float4 *smemTris, uint32_t nTris, V3 o, V3 d, float tFar,
+                                               Counters &cnt) {
   Hit r = hit_none();
   uint32_t best = 0;
   for (uint32_t k = 0; k < nTris; ++k) {
     if (COUNT) cnt.bvh_tris++;
     const float4 a = smemTris[3 * k], bq = smemTris[3 * k + 1], cq = smemTris[3 * k + 2];
     float th;
-    if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && (!r.hitten || r.t > th)) {
+    // th <= tFar stands in for the reference's box culling: its leaf boxes hug the faces of a small mesh, so a hit
+    // beyond tFar (= the depth already in the framebuffer) never survives there, while hits in front of tNear and
+    // behind the origin do (triangle hits themselves are not range-checked).  Checked against the compiled
+    // reference on the cube from outside and inside, cleared and pre-filled depth (tests/test_host_emul.py).
+    if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && th <= tFar && (!r.hitten || r.t > th)) {
       r.hitten = true;
       r.t = th;
       best = k;

@@ -283,3 +283,28 @@ def test_brute_force_path_golden_prefilled_frames():
         c0 = np.full((c["H"], c["W"]), 0x11223344, np.uint32)
         col, t, _, _ = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"]), color=c0, t=t0)
         assert util.same_bits(t, c["t_prefilled"]) and np.array_equal(col, c["color_prefilled"]), key
+
+
+def test_device_source_on_cpu_large_standins():
+    """BASELINE configs[2] / [3] stand-ins (257^3 grid in both layouts, depth-8 octree with 0.6 M nodes) on seeded
+    cameras, visit counters included: the deeper tree and the larger index arithmetic, which the GPU tests only see
+    from the default camera."""
+    W, H = 72, 48
+    pinv = rt.host_projection(W, H)[1]
+    a = G.scene_arrays("octree_d8")
+    s, ps = E.EmulScene.octree(a["nodes36"]), P.Scene.octree(a["nodes36"])
+    for k, pos, vinv in seeded_cameras(40, seed=12):
+        col, t, _, cnt = s.render(rt.make_frame(pos, vinv, pinv, W, H, mode=rt.SHADE_LAMBERT))
+        pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, mode=P.MODE_LAMBERT, want_counters=True)
+        assert util.same_bits(t, pt) and np.array_equal(col, pc), f"octree_d8 camera {k}"
+        for cn, pn in COUNTERS["octree"].items():
+            assert cnt[cn] == pcnt[pn], f"octree_d8 camera {k}: counter {cn}"
+    a = G.scene_arrays("example_grid_x4")
+    lin, bri, ps = E.EmulScene.grid(a["values"]), E.EmulScene.grid(a["values"], bricks=True), P.Scene.grid(a["values"])
+    for k, pos, vinv in seeded_cameras(30, seed=13):
+        f = rt.make_frame(pos, vinv, pinv, W, H)
+        pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, want_counters=True)
+        for s in (lin, bri):
+            col, t, _, cnt = s.render(f)
+            assert util.same_bits(t, pt) and np.array_equal(col, pc), f"grid x4 camera {k}"
+            assert cnt["grid_samples"] == pcnt["gridSdf"]

@@ -54,6 +54,8 @@ def lib():
         L.emul_grid_bricks.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32]
         L.emul_intersect.restype = C.c_int
         L.emul_intersect.argtypes = [vp, vp, vp, C.c_uint32, C.c_float, C.c_float, C.c_int, C.c_float, vp, vp, vp, vp]
+        L.emul_work_map.restype = C.c_int
+        L.emul_work_map.argtypes = [vp, vp, vp]
         L.emul_octree.restype = vp
         L.emul_octree.argtypes = [vp, C.c_uint32]
         L.emul_mesh.restype = vp
@@ -138,3 +140,9 @@ class EmulScene:
                                   float(plane_y or 0.0), _p(hit), _p(t), _p(nrm), _p(prim))
         assert rc == 0
         return hit.astype(bool), t, nrm, prim
+
+    def work_map(self, frame):
+        """Per-pixel work of the primary rays -> uint32 [H, W, 4]: inner visits, leaf visits, SDF samples, triangle tests."""
+        w = np.zeros((frame.height, frame.width, 4), np.uint32)
+        assert lib().emul_work_map(self._h, C.byref(frame), _p(w)) == 0
+        return w

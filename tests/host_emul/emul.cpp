@@ -242,6 +242,37 @@ int emul_intersect(const EmulScene *e, const float *origins, const float *dirs, 
   return 0;
 }
 
+// Per-pixel work of a primary-ray frame (analysis of SIMD efficiency under different pixel -> warp mappings,
+// tools/warp_efficiency.py): work[px * 4 + {0,1,2,3}] = inner-node visits, leaf visits, SDF samples, triangle tests.
+int emul_work_map(const EmulScene *e, const rt_frame *fr, uint32_t *work) {
+  if (!e || !fr || !work) return -1;
+  rt_frame one = *fr;
+  const SceneDev &s = e->dev;
+  const float4 *tris = reinterpret_cast<const float4 *>(s.mesh.tris);
+  FrameDev f{};
+  std::memcpy(f.ray_pos, one.ray_pos, sizeof f.ray_pos);
+  std::memcpy(f.view_inv, one.view_inv, sizeof f.view_inv);
+  std::memcpy(f.proj_inv, one.proj_inv, sizeof f.proj_inv);
+  f.W = one.width; f.H = one.height;
+  f.t_near = 0.01f; f.t_far = 100.0f;
+  for (uint32_t row = 0; row < f.H; ++row)
+    for (uint32_t x = 0; x < f.W; ++x) {
+      emul::Counters c = {};
+      const emul::V3 o = emul::mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
+      const emul::V3 d = emul::eye_ray(f, (int)x, (int)(f.H - 1u - row));
+      if (s.kind == RT_SCENE_GRID) emul::scene_intersect<emul::KIND_GRID, true>(s, nullptr, false, 0.f, o, d, f.t_near, f.t_far, c);
+      else if (s.kind == RT_SCENE_OCTREE) emul::scene_intersect<emul::KIND_OCTREE, true>(s, nullptr, false, 0.f, o, d, f.t_near, f.t_far, c);
+      else if (s.mesh.brute) emul::scene_intersect<emul::KIND_BRUTE, true>(s, tris, false, 0.f, o, d, f.t_near, f.t_far, c);
+      else emul::scene_intersect<emul::KIND_BVH, true>(s, nullptr, false, 0.f, o, d, f.t_near, f.t_far, c);
+      uint32_t *w = work + ((size_t)row * f.W + x) * 4;
+      w[0] = c.oct_inner + c.bvh_inner;
+      w[1] = c.oct_leaf + c.bvh_leaf;
+      w[2] = c.grid_samples + c.oct_leaf_samples;
+      w[3] = c.bvh_tris;
+    }
+  return 0;
+}
+
 // Renderer::draw over the whole frame.  frame = the rt_frame of include/rt_b200.h (band fields ignored).
 // counters: 9 x u64 in rt_counters order, or null.
 int emul_render(const EmulScene *e, const rt_frame *fr, uint32_t *color, float *t, uint32_t *prim,

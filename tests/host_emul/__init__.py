@@ -54,6 +54,9 @@ def lib():
         L.emul_grid_bricks.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32]
         L.emul_intersect.restype = C.c_int
         L.emul_intersect.argtypes = [vp, vp, vp, C.c_uint32, C.c_float, C.c_float, C.c_int, C.c_float, vp, vp, vp, vp]
+        for fn in (L.emul_intersect_walk, L.emul_intersect_octree_counted):
+            fn.restype = C.c_int
+            fn.argtypes = [vp, vp, vp, C.c_uint32, C.c_float, C.c_float, vp, vp, vp, vp]
         L.emul_work_map.restype = C.c_int
         L.emul_work_map.argtypes = [vp, vp, vp]
         L.emul_octree.restype = vp
@@ -146,3 +149,14 @@ class EmulScene:
         w = np.zeros((frame.height, frame.width, 4), np.uint32)
         assert lib().emul_work_map(self._h, C.byref(frame), _p(w)) == 0
         return w
+
+    def octree_rays(self, origins, dirs, t_near=0.01, t_far=100.0, walk=False):
+        """Octree scenes: oct_intersect (walk=False) or the resumable OctWalk form driven to completion (walk=True)
+        -> (hit, t, normal, (inner visits, leaf visits, leaf samples))."""
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        hit, t, nrm, cnt = np.zeros(n, np.uint8), np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros(3, np.uint64)
+        fn = lib().emul_intersect_walk if walk else lib().emul_intersect_octree_counted
+        assert fn(self._h, _p(o), _p(d), n, t_near, t_far, _p(hit), _p(t), _p(nrm), _p(cnt)) == 0
+        return hit.astype(bool), t, nrm, tuple(int(x) for x in cnt)

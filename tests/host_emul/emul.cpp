@@ -242,6 +242,61 @@ int emul_intersect(const EmulScene *e, const float *origins, const float *dirs, 
   return 0;
 }
 
+// The resumable octree walk (OctWalk: what render_octree_compact_kernel drives lane by lane) run to completion for one
+// ray at a time: begin, then step / leaf until a leaf hits or the walk is done.  Octree scenes with an inner root only.
+int emul_intersect_walk(const EmulScene *e, const float *origins, const float *dirs, uint32_t n, float t_near,
+                        float t_far, uint8_t *hit, float *t, float *normal, unsigned long long *counters3) {
+  if (!e || e->dev.kind != RT_SCENE_OCTREE || !e->dev.oct.root_inner) return -1;
+  const OctreeDev &oc = e->dev.oct;
+  emul::Counters cnt = {};
+  for (uint32_t i = 0; i < n; ++i) {
+    const emul::V3 o = emul::mk3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
+    const emul::V3 d = emul::mk3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+    emul::OctWalk w;
+    emul::Hit h = emul::hit_none();
+    emul::oct_walk_begin<true>(w, oc, o, d, t_near, t_far, cnt);
+    for (;;) {
+      const int r = emul::oct_walk_step<true>(w, oc, o, t_near, cnt);
+      if (r == emul::OCT_WALK_DONE) break;
+      if (r == emul::OCT_WALK_LEAF && emul::oct_walk_leaf<true>(w, oc, o, t_near, h, cnt)) break;
+    }
+    hit[i] = h.hitten ? 1 : 0;
+    t[i] = h.t;
+    normal[3 * i] = h.normal.x;
+    normal[3 * i + 1] = h.normal.y;
+    normal[3 * i + 2] = h.normal.z;
+  }
+  if (counters3) {
+    counters3[0] = cnt.oct_inner;
+    counters3[1] = cnt.oct_leaf;
+    counters3[2] = cnt.oct_leaf_samples;
+  }
+  return 0;
+}
+
+// the same rays through oct_intersect, with the same three counters
+int emul_intersect_octree_counted(const EmulScene *e, const float *origins, const float *dirs, uint32_t n, float t_near,
+                                  float t_far, uint8_t *hit, float *t, float *normal, unsigned long long *counters3) {
+  if (!e || e->dev.kind != RT_SCENE_OCTREE) return -1;
+  emul::Counters cnt = {};
+  for (uint32_t i = 0; i < n; ++i) {
+    const emul::V3 o = emul::mk3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
+    const emul::V3 d = emul::mk3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+    emul::Hit h = emul::oct_intersect<true>(e->dev.oct, o, d, t_near, t_far, cnt);
+    hit[i] = h.hitten ? 1 : 0;
+    t[i] = h.t;
+    normal[3 * i] = h.normal.x;
+    normal[3 * i + 1] = h.normal.y;
+    normal[3 * i + 2] = h.normal.z;
+  }
+  if (counters3) {
+    counters3[0] = cnt.oct_inner;
+    counters3[1] = cnt.oct_leaf;
+    counters3[2] = cnt.oct_leaf_samples;
+  }
+  return 0;
+}
+
 // Per-pixel work of a primary-ray frame (analysis of SIMD efficiency under different pixel -> warp mappings,
 // tools/warp_efficiency.py): work[px * 4 + {0,1,2,3}] = inner-node visits, leaf visits, SDF samples, triangle tests.
 int emul_work_map(const EmulScene *e, const rt_frame *fr, uint32_t *work) {

@@ -308,3 +308,17 @@ def test_device_source_on_cpu_large_standins():
             col, t, _, cnt = s.render(f)
             assert util.same_bits(t, pt) and np.array_equal(col, pc), f"grid x4 camera {k}"
             assert cnt["grid_samples"] == pcnt["gridSdf"]
+
+
+@pytest.mark.parametrize("name", ("sdf_6", "sdf_5", "octree_d8"))
+def test_resumable_octree_walk_equals_the_plain_traversal(name):
+    """OctWalk (begin / step / leaf: the lane state machine of render_octree_compact_kernel) driven to completion for one
+    ray at a time visits the same nodes, marches the same leaves and returns the same hits as oct_intersect."""
+    a = G.scene_arrays(name)
+    s = E.EmulScene.octree(a["nodes36"])
+    o, d = _ray_batch(seed=21, n_random=4000)
+    for t_near, t_far in ((0.01, 100.0), (0.3, 2.2)):
+        h0, t0, n0, c0 = s.octree_rays(o, d, t_near, t_far, walk=False)
+        h1, t1, n1, c1 = s.octree_rays(o, d, t_near, t_far, walk=True)
+        assert np.array_equal(h0, h1) and util.same_bits(t0, t1) and util.same_bits(n0[h0], n1[h0])
+        assert c0 == c1, f"{name}: visit counters {c0} vs {c1}"

@@ -452,6 +452,10 @@ def run_cuda(args):
                             "the render kernel stores its tiles into the pinned host framebuffer over PCIe "
                             "(128-byte bulk stores, one launch, no copy engine)"),
                "d2h_floor_ms_at_56GBps": 8 * px / 56e9 * 1e3,
+               # the host call is bound by the PCIe link, not by HBM: achieved = bytes that crossed it / wall time of the
+               # call; peak = the copy-engine D2H rate measured on this pool's boxes (tools/pcie_probe.py, Gen5 x16)
+               "link": {"bound": "pcie", "achieved": 8 * px / (e2e_ms * 1e-3) / 1e9, "peak": 56.0, "unit": "GB/s",
+                        "frac": 8 * px / (e2e_ms * 1e-3) / 1e9 / 56.0},
                "after_cpu_read_of_colour": {"value": px / blit_ms / 1e3, "ms_per_step": blit_ms},
                "after_cpu_rewrite_of_both_buffers": {"value": px / dirty_ms / 1e3, "ms_per_step": dirty_ms,
                                                      "note": "dirty CPU cache lines slow copy-engine writes (0.40 -> 0.58 ms at 1080p, "

@@ -322,3 +322,98 @@ def test_resumable_octree_walk_equals_the_plain_traversal(name):
         h1, t1, n1, c1 = s.octree_rays(o, d, t_near, t_far, walk=True)
         assert np.array_equal(h0, h1) and util.same_bits(t0, t1) and util.same_bits(n0[h0], n1[h0])
         assert c0 == c1, f"{name}: visit counters {c0} vs {c1}"
+
+
+def _random_octree(rng, max_depth, p_inner):
+    """A structurally valid random octree in the file's 36-byte records (8 children contiguous at childrenOffset), with
+    leaf values drawn from a mix that hits every classification rule: empty markers (all 1000 / all 0), all-positive
+    leaves just above and below the 1e-4 threshold, sign changes, exact zeros at corners, large magnitudes."""
+    vals, offs = [np.zeros(8, np.float32)], [0]
+    frontier = [(0, 0)]
+    while frontier:
+        nxt = []
+        for node, depth in frontier:
+            if depth < max_depth and (depth == 0 or rng.random() < p_inner):
+                first = len(vals)
+                offs[node] = first
+                for _ in range(8):
+                    vals.append(np.zeros(8, np.float32))
+                    offs.append(0)
+                    nxt.append((len(vals) - 1, depth + 1))
+            else:
+                kind = rng.integers(0, 8)
+                if kind == 0:
+                    v = np.full(8, 1000.0)
+                elif kind == 1:
+                    v = np.zeros(8)
+                elif kind == 2:
+                    v = rng.uniform(1e-4, 3e-4, 8)          # all >= 1e-4: rejected without a march
+                elif kind == 3:
+                    v = rng.uniform(0.5e-4, 2e-4, 8)        # straddles the threshold
+                elif kind == 4:
+                    v = rng.uniform(-0.2, 0.3, 8)
+                    v[rng.integers(0, 8)] = 0.0             # an exact zero at a corner
+                elif kind == 5:
+                    v = rng.uniform(-0.05, 0.6, 8)
+                elif kind == 6:
+                    v = rng.uniform(5.0, 20.0, 8)           # > 10 everywhere or mixed around it
+                else:
+                    v = rng.normal(0.1, 0.2, 8)
+                vals[node] = v.astype(np.float32)
+        frontier = nxt
+    rec = np.zeros((len(vals), 36), np.uint8)
+    rec[:, :32] = np.asarray(vals, np.float32).view(np.uint8).reshape(-1, 32)
+    rec[:, 32:] = np.asarray(offs, np.uint32).view(np.uint8).reshape(-1, 4)
+    return rec
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_octrees_vs_oracle(seed):
+    """Structures the shipped files never contain (sparse and lopsided trees, leaves at every depth, every leaf class
+    next to every other): frames with counters, single rays incl. axis-parallel ones, and the resumable walk."""
+    rng = np.random.default_rng(900 + seed)
+    nodes = _random_octree(rng, max_depth=int(rng.integers(1, 5)), p_inner=float(rng.uniform(0.2, 0.7)))
+    s, ps = E.EmulScene.octree(nodes), P.Scene.octree(nodes)
+    W, H = 48, 32
+    pinv = rt.host_projection(W, H)[1]
+    for k, pos, vinv in seeded_cameras(10, seed=seed):
+        col, t, _, cnt = s.render(rt.make_frame(pos, vinv, pinv, W, H))
+        pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, want_counters=True)
+        assert util.same_bits(t, pt) and np.array_equal(col, pc), f"seed {seed} camera {k} ({nodes.shape[0]} nodes)"
+        for cn, pn in COUNTERS["octree"].items():
+            assert cnt[cn] == pcnt[pn], f"seed {seed} camera {k}: counter {cn} {cnt[cn]} != {pcnt[pn]}"
+    o, d = _ray_batch(seed=seed, n_random=300)
+    hit, t, nrm, _ = s.intersect(o, d)
+    for i in range(o.shape[0]):
+        h, pt, pn, _ = ps.intersect(o[i], d[i])
+        assert bool(hit[i]) == h and (not h or (util.same_bits(t[i], pt) and util.same_bits(nrm[i], pn))), f"seed {seed} ray {i}"
+    h1, t1, n1, c1 = s.octree_rays(o, d, walk=True)
+    h0, t0, n0, c0 = s.octree_rays(o, d, walk=False)
+    assert np.array_equal(h0, h1) and util.same_bits(t0, t1) and c0 == c1
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_grids_vs_oracle(seed):
+    """Grids the shipped file is not: 2 samples on an axis, non-cubic sizes, sizes that are not a multiple of the brick
+    edge, random (non-distance) fields with the surface touching the box faces; both layouts."""
+    rng = np.random.default_rng(500 + seed)
+    size = tuple(int(x) for x in rng.integers(2, 12, size=3))
+    x, y, z = np.meshgrid(*(np.linspace(-1, 1, n) for n in size), indexing="ij")
+    c = rng.uniform(-0.5, 0.5, 3)
+    field = np.sqrt((x - c[0]) ** 2 + (y - c[1]) ** 2 + (z - c[2]) ** 2) - rng.uniform(0.3, 1.2)
+    field += rng.normal(0, 0.05, size)
+    v = np.ascontiguousarray(field, np.float32)
+    lin, bri, ps = E.EmulScene.grid(v), E.EmulScene.grid(v, bricks=True), P.Scene.grid(v)
+    W, H = 48, 32
+    pinv = rt.host_projection(W, H)[1]
+    for k, pos, vinv in seeded_cameras(10, seed=seed):
+        pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, mode=P.MODE_LAMBERT, want_counters=True)
+        for s in (lin, bri):
+            col, t, _, cnt = s.render(rt.make_frame(pos, vinv, pinv, W, H, mode=rt.SHADE_LAMBERT))
+            assert util.same_bits(t, pt) and np.array_equal(col, pc), f"seed {seed} size {size} camera {k}"
+            assert cnt["grid_samples"] == pcnt["gridSdf"]
+    o, d = _ray_batch(seed=seed, n_random=300)
+    hit, t, nrm, _ = lin.intersect(o, d)
+    for i in range(o.shape[0]):
+        h, pt, pn, _ = ps.intersect(o[i], d[i])
+        assert bool(hit[i]) == h and (not h or (util.same_bits(t[i], pt) and util.same_bits(nrm[i], pn))), f"seed {seed} ray {i}"

@@ -158,3 +158,40 @@ def test_port_vs_compiled_reference_on_seeded_cameras(golden, name, n_cams):
             col, t, _prim, _ = s.render(pos, view_inv, proj_inv, W, H, mode=mode_port)
             assert util.same_bits(t, want_t), f"{name} camera {k} {cam}: depth differs"
             assert np.array_equal(col, want_c), f"{name} camera {k} {cam}: colour differs (mode {mode_port})"
+
+
+@pytest.mark.ref
+@pytest.mark.parametrize("seed", range(8))
+def test_port_vs_compiled_reference_on_random_scenes(seed):
+    """The restatement against the compiled reference on scenes neither ships: random octrees (every leaf class at every
+    depth) and random non-cubic grids down to 2 samples per axis.  Frames in all shadings and single rays."""
+    from oracle import ref_oracle as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    from tests.test_host_emul import _random_octree, _ray_batch
+    ro = R.RefOracle()
+    rng = np.random.default_rng(4200 + seed)
+    nodes = _random_octree(rng, max_depth=int(rng.integers(1, 5)), p_inner=float(rng.uniform(0.2, 0.7)))
+    size = tuple(int(x) for x in rng.integers(2, 12, size=3))
+    x, y, z = np.meshgrid(*(np.linspace(-1, 1, n) for n in size), indexing="ij")
+    field = np.sqrt((x - 0.2) ** 2 + (y + 0.1) ** 2 + z ** 2) - rng.uniform(0.3, 1.2) + rng.normal(0, 0.05, size)
+    grid = np.ascontiguousarray(field, np.float32)
+    W, H = 48, 32
+    proj_inv = ro.projection(W, H)[1]
+    for what, ref, s in (("octree", ro.octree(nodes), P.Scene.octree(nodes)), ("grid", ro.grid(grid), P.Scene.grid(grid))):
+        for k in range(8):
+            v = rng.normal(size=3)
+            eye = tuple(float(c) for c in float(rng.choice([0.3, 0.9, 1.6, 2.5])) * v / np.linalg.norm(v))
+            cam = R.CamSpec(eye=eye, target=tuple(float(c) for c in rng.uniform(-0.3, 0.3, size=3)), lock_up=bool(k % 2))
+            pos, _view, view_inv = ro.camera(cam)
+            mode_ref, mode_port = ((R.MODE_NORMAL, P.MODE_NORMAL), (R.MODE_LAMBERT, P.MODE_LAMBERT))[k % 2]
+            want_c, want_t, _ = ref.render(cam, W, H, proj_inv=proj_inv, mode=mode_ref)
+            col, t, _prim, _ = s.render(pos, view_inv, proj_inv, W, H, mode=mode_port)
+            assert util.same_bits(t, want_t) and np.array_equal(col, want_c), f"seed {seed} {what} camera {k}"
+        o, d = _ray_batch(seed=seed, n_random=200)
+        for i in range(o.shape[0]):
+            r = ref.intersect(o[i], d[i])
+            h, pt, pn, _ = s.intersect(o[i], d[i])
+            assert bool(r[0]) == h, f"seed {seed} {what} ray {i} o={o[i]} d={d[i]}"
+            if h:
+                assert util.same_bits(pt, r[1]) and util.same_bits(pn, r[2]), f"seed {seed} {what} ray {i}"

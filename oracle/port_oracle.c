@@ -69,6 +69,8 @@ typedef struct {
   /* optional checkerboard ground plane y = planeY: SceneUnion(model, Plane({0,1,0}, planeY)), main.cpp:189-190 */
   int32_t hasPlane;
   float planeY;
+  /* meshes without a BVH (mesh_brute): bounding box of the triangles' vertices (after the division by w) */
+  float bboxMin[3], bboxMax[3];
 } PortScene;
 
 typedef struct {
@@ -458,10 +460,19 @@ static BvhHit bvh_node(const PortScene *s, uint32_t index, v3 o, v3 d, float tNe
  * nBvhNodes' place.  The one thing a tree adds to the answer is box culling against [tNear, tFar]
  * (triangles_raytracing.cpp:266-297): a hit beyond tFar (the depth already in the framebuffer) lies in leaf boxes that
  * start beyond tFar and is never reached, while hits before tNear or behind the origin are (their boxes straddle the
- * origin).  `th <= tFar` restates that; checked against the compiled reference on the cube, from outside and inside,
- * cleared and pre-filled depth buffers (tests/test_host_emul.py, tests/test_oracle_port.py). */
-static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, float tFar, PortCounters *cnt) {
+ * origin).  Two tree-independent conditions restate that: the ray must pass intersect_box_8's test (slab_lane) on the
+ * mesh's bounding box, inside which every box of any tree lies (a ray looking away from the mesh, or stopped by tFar
+ * in front of it, reaches no leaf), and `th <= tFar`.  Checked against the compiled reference on the cube: frames from
+ * outside and inside, looking at and away from it, cleared and pre-filled depth buffers, and single rays with
+ * arbitrary ranges (tests/test_oracle_port.py, tests/test_host_emul.py). */
+static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, float tNear, float tFar, PortCounters *cnt) {
   BvhHit result = {0, INFINITY, 0};
+  {
+    v3 inv = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
+    if (slab_lane(s->bboxMin[0], s->bboxMin[1], s->bboxMin[2], s->bboxMax[0], s->bboxMax[1], s->bboxMax[2], o, inv, tNear,
+                  tFar) < 0.0f)
+      return result;
+  }
   uint32_t nTri = s->bvhNodeBytes; /* triangle count when bvhNodes == NULL */
   for (uint32_t k = 0; k < nTri; ++k) {
     if (cnt) cnt->bvhTris++;
@@ -480,7 +491,7 @@ static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, float tFar, PortCounter
 
 static Hit mesh_intersect(const PortScene *s, v3 o, v3 d, float tNear, float tFar, PortCounters *cnt) {
   Hit r = hit_none();
-  BvhHit b = s->bvhNodes ? bvh_node(s, 0, o, d, tNear, tFar, cnt) : mesh_brute(s, o, d, tFar, cnt);
+  BvhHit b = s->bvhNodes ? bvh_node(s, 0, o, d, tNear, tFar, cnt) : mesh_brute(s, o, d, tNear, tFar, cnt);
   if (!b.hitten) return r;
   r.hitten = 1;
   r.t = b.t;

@@ -28,6 +28,7 @@ class PortScene(C.Structure):
         ("vpos4", C.c_void_p), ("indices", C.c_void_p), ("bvhNodes", C.c_void_p),
         ("nBvhNodes", C.c_uint32), ("bvhNodeBytes", C.c_uint32), ("primOfPermuted", C.c_void_p),
         ("hasPlane", C.c_int32), ("planeY", C.c_float),
+        ("bboxMin", C.c_float * 3), ("bboxMax", C.c_float * 3),
     ]
 
 
@@ -152,6 +153,10 @@ class Scene:
         s.c.bvhNodes = None
         s.c.nBvhNodes = 0
         s.c.bvhNodeBytes = i.size // 3  # triangle count (see port_oracle.c mesh_brute)
+        used = v[i]                                      # vertices the triangles reference
+        p = (used[:, :3] / used[:, 3:4]).astype(np.float32)  # the division by w of triangles_raytracing.cpp:307-309
+        s.c.bboxMin[:] = [float(x) for x in p.min(axis=0)]
+        s.c.bboxMax[:] = [float(x) for x in p.max(axis=0)]
         return s
 
     def with_plane(self, y: float) -> "Scene":

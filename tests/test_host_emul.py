@@ -245,9 +245,12 @@ def test_device_source_on_cpu_single_rays_vs_oracle(name):
 
 
 @pytest.mark.ref
-def test_brute_force_path_matches_the_reference_with_a_prefilled_depth_buffer():
-    """The <= 32-triangle kernel has no tree, the reference culls by its leaf boxes: `t <= tFar` per triangle reproduces
-    it on the cube (BASELINE configs[0]) from outside and inside, on cleared and pre-filled depth buffers."""
+def test_brute_force_path_matches_the_reference():
+    """The <= 32-triangle kernel has no tree; the reference reaches triangles only through boxes that pass its slab test.
+    The mesh-bounding-box cull plus `t <= tFar` per triangle reproduce it on the cube (BASELINE configs[0]): frames from
+    outside, from just outside the faces and from inside, looking at the cube and away from it, on cleared and
+    pre-filled depth buffers, and single rays with arbitrary [tNear, tFar].  Both the kernel source and the oracle's
+    every-triangle loop."""
     from oracle import ref_oracle as R
     if not R.available():
         pytest.skip("oracle/_ref not built")
@@ -255,23 +258,41 @@ def test_brute_force_path_matches_the_reference_with_a_prefilled_depth_buffer():
     ro = R.RefOracle()
     ref = ro.mesh(a["vpos4"], a["indices"])
     s = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=True)
+    ps = P.Scene.mesh_brute(a["vpos4"], a["indices"])
     W, H = 64, 40
     pinv = ro.projection(W, H)[1]
     rng = np.random.default_rng(3)
-    for radii in ((1.8, 2.5, 4.0), (0.2, 0.5, 0.9)):
-        for prefill in (True, False):
-            for k in range(30):
-                v = rng.normal(size=3)
-                eye = tuple(float(x) for x in float(rng.choice(radii)) * v / np.linalg.norm(v))
-                cam = R.CamSpec(eye=eye, target=tuple(float(x) for x in rng.uniform(-0.3, 0.3, size=3)), lock_up=bool(k % 2))
-                pos, _view, vinv = ro.camera(cam)
-                t0 = (rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
-                      if prefill else np.full((H, W), np.inf, np.float32))
-                c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
-                want_c, want_t, _ = ref.render(cam, W, H, proj_inv=pinv, color=c0, t=t0)
-                col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
-                assert util.same_bits(t, want_t), f"radii {radii} prefill {prefill} camera {k}: depth differs"
-                assert (col != want_c).sum() <= 0.01 * W * H  # exact-t ties on the cube's shared edges
+    for radii in ((1.8, 2.5, 4.0), (1.05, 1.2), (0.2, 0.5, 0.9)):
+        for prefill in (False, True):
+            for away in (False, True):
+                for k in range(12):
+                    v = rng.normal(size=3)
+                    v /= np.linalg.norm(v)
+                    r = float(rng.choice(radii))
+                    eye = tuple(float(x) for x in r * v)
+                    target = (tuple(float(x) for x in 2.5 * r * v + rng.uniform(-0.5, 0.5, 3)) if away
+                              else tuple(float(x) for x in rng.uniform(-0.3, 0.3, size=3)))
+                    cam = R.CamSpec(eye=eye, target=target, lock_up=bool(k % 2))
+                    pos, _view, vinv = ro.camera(cam)
+                    t0 = (rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
+                          if prefill else np.full((H, W), np.inf, np.float32))
+                    c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
+                    want_c, want_t, _ = ref.render(cam, W, H, proj_inv=pinv, color=c0, t=t0)
+                    col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
+                    pc, pt, _, _ = ps.render(pos, vinv, pinv, W, H, color=c0, t=t0)
+                    where = f"radii {radii} prefill {prefill} away {away} camera {k}"
+                    assert util.same_bits(t, want_t), f"kernel source, {where}: depth differs"
+                    assert util.same_bits(pt, want_t), f"oracle, {where}: depth differs"
+                    assert (col != want_c).sum() <= 0.01 * W * H and (pc != want_c).sum() <= 0.01 * W * H  # edge ties
+    o, d = _ray_batch(seed=4, n_random=800)
+    for t_near, t_far in ((0.01, 100.0), (0.3, 2.2), (1.0, 1.6)):
+        hit, t, _, _ = s.intersect(o, d, t_near, t_far)
+        for i in range(o.shape[0]):
+            r = ref.intersect(o[i], d[i], t_near, t_far)
+            h, pt, _, _ = ps.intersect(o[i], d[i], t_near, t_far)
+            assert bool(hit[i]) == bool(r[0]) == h, f"ray {i} o={o[i]} d={d[i]} [{t_near}, {t_far}]"
+            if h:
+                assert util.same_bits(t[i], r[1]) and util.same_bits(pt, r[1]), f"ray {i} [{t_near}, {t_far}]"
 
 
 def test_brute_force_path_golden_prefilled_frames():

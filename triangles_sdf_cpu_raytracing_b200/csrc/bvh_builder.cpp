@@ -251,6 +251,16 @@ bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, u
   out.stack_need = 0;
   if (brute) {
     out.tris = std::move(all);  // original order: ties keep the lowest prim id
+    // one node whose lane 0 is the mesh's bounding box: the brute-force kernel culls a ray against it the way the
+    // reference culls against its child boxes (every one of them lies inside this box)
+    BvhNode root{};
+    for (int l = 0; l < 8; ++l) root.child[l] = BVH_EMPTY;
+    for (int a = 0; a < 3; ++a) {
+      root.lo[a][0] = total.lo[a];
+      root.hi[a][0] = total.hi[a];
+    }
+    root.child[0] = BVH_LEAF_BIT;
+    out.nodes.push_back(root);
     return true;
   }
   bld.bin.reserve(2 * (size_t)nTri / LEAF_MAX + 16);

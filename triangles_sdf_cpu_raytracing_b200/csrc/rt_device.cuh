@@ -796,9 +796,21 @@ done:
 
 // Every triangle against the ray, triangles staged in shared memory by the kernel (smem = n_tris x 3 float4).
 template <bool COUNT>
-__device__ __forceinline__ Hit brute_intersect(const float4 *smemTris, uint32_t nTris, V3 o, V3 d, float tFar,
-                                               Counters &cnt) {
+__device__ __forceinline__ Hit brute_intersect(const MeshDev &m, const float4 *smemTris, V3 o, V3 d, float tNear,
+                                               float tFar, Counters &cnt) {
   Hit r = hit_none();
+  const uint32_t nTris = m.n_tris;
+  // The reference only reaches triangles through boxes that pass intersect_box_8 against [tNear, tFar] (a box wholly
+  // behind the origin or beyond tFar is culled, triangles_raytracing.cpp:266-297); all of them lie inside the mesh's
+  // bounding box, which is lane 0 of the single node a brute-force scene carries: a ray that fails this test hits
+  // nothing there (looking away from the mesh, or the framebuffer already holding a nearer depth).
+  {
+    const BvhNode *n = m.nodes;
+    const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    if (slab_lane<false>(__ldg(&n->lo[0][0]), __ldg(&n->lo[1][0]), __ldg(&n->lo[2][0]), __ldg(&n->hi[0][0]),
+                         __ldg(&n->hi[1][0]), __ldg(&n->hi[2][0]), o, inv, tNear, tFar) < 0.0f)
+      return r;
+  }
   uint32_t best = 0;
   for (uint32_t k = 0; k < nTris; ++k) {
     if (COUNT) cnt.bvh_tris++;

@@ -14,7 +14,7 @@ __device__ __forceinline__ Hit model_intersect(const SceneDev &s, const float4 *
   if (KIND == KIND_GRID_BRICKS) return grid_intersect<true, COUNT>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_OCTREE) return oct_intersect<COUNT>(s.oct, o, d, tNear, tFar, cnt);
   if (KIND == KIND_BVH) return bvh_intersect<COUNT>(s.mesh, o, d, tNear, tFar, cnt);
-  return brute_intersect<COUNT>(smemTris, s.mesh.n_tris, o, d, tFar, cnt);
+  return brute_intersect<COUNT>(s.mesh, smemTris, o, d, tNear, tFar, cnt);
 }
 
 template <int KIND, bool COUNT>

@@ -90,21 +90,30 @@ def test_device_source_on_cpu_vs_oracle_seeded_cameras_sdf(name, n_cams):
             assert cnt[cn] == pcnt[pn], f"{name} camera {k}: counter {cn} {cnt[cn]} != {pcnt[pn]}"
 
 
-@pytest.mark.parametrize("name", ("example_grid", "sdf_6"))
+@pytest.mark.parametrize("name", ("example_grid", "sdf_6", "sdf_5"))
 def test_device_source_on_cpu_in_out_depth_buffer(name):
-    """raytracing.cpp:90-94: a pixel is replaced only by a nearer hit; the previous depth also bounds the march."""
+    """raytracing.cpp:90-94: a pixel is replaced only by a nearer hit; the previous depth also bounds the march.  Depths
+    in front of tNear and beyond tFar included, eyes inside the box included, with and without the ground plane and the
+    secondary rays."""
     s, _ = emul_scene(name)
     ps = util.port_scene(G, name)
     W, H = 64, 40
     pinv = rt.host_projection(W, H)[1]
     rng = np.random.default_rng(5)
-    for k, pos, vinv in seeded_cameras(12, seed=77, radii=(1.6, 2.5)):
-        t0 = rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
+    replaced = kept = 0
+    for k, pos, vinv in seeded_cameras(60, seed=78):
+        t0 = rng.choice(np.array([np.inf, 0.005, 0.05, 0.5, 1.2, 2.0, 2.6, 3.5, 150.0], np.float32), size=(H, W)).astype(np.float32)
         c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
-        col, t, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
-        pc, pt, _, _ = ps.render(pos, vinv, pinv, W, H, color=c0, t=t0)
+        plane = k % 4 == 0
+        f = rt.make_frame(pos, vinv, pinv, W, H, mode=rt.SHADE_LAMBERT, shadows=plane, reflections=plane,
+                          plane_y=-1.0 if plane else None)
+        col, t, _, _ = s.render(f, color=c0, t=t0)
+        sc = ps.with_plane(-1.0) if plane else ps
+        pc, pt, _, _ = sc.render(pos, vinv, pinv, W, H, mode=P.MODE_LAMBERT, shadows=plane, reflections=plane, color=c0, t=t0)
         assert util.same_bits(t, pt) and np.array_equal(col, pc), f"{name} camera {k}"
-        assert (t != t0).any() and (t == t0).any()  # some pixels replaced, some kept
+        replaced += int((t != t0).sum())
+        kept += int((t == t0).sum())
+    assert replaced > 0 and kept > 0
 
 
 @pytest.mark.parametrize("name,n_cams", (("cube", 60), ("stanford-bunny", 12), ("spot", 12), ("as1-oc-214", 12)))

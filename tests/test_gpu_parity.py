@@ -354,10 +354,8 @@ for key in ("example_grid|default|160x90", "sdf_6|default|160x90", "stanford-bun
                                    C.byref(dms), C.byref(tms), None))
     assert util.same_bits(tn[:, :W // 2], c["t"][:, :W // 2]), key
     assert np.array_equal(cn[:, :W // 2], c["color_normal"][:, :W // 2]), key
-    # (the 12-triangle cube goes through the brute-force kernel: triangle hits are not range-checked, SURVEY T6, and
-    # there is no box test to cull them by, so there the nearer surface does not survive: observed, not asserted)
-    if not key.startswith("cube"):
-        assert np.all(cn[:, W // 2:] == 7) and np.all(tn[:, W // 2:] == np.float32(1e-3)), key
+    # (also for the 12-triangle cube's brute-force kernel: its mesh-bounding-box cull stands in for the tree's boxes)
+    assert np.all(cn[:, W // 2:] == 7) and np.all(tn[:, W // 2:] == np.float32(1e-3)), key
 print("zero-copy ok")
 """
     env = dict(os.environ, RT_HOST_ZEROCOPY=mode)

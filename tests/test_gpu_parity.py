@@ -407,3 +407,38 @@ def test_pinned_framebuffer_and_registered_arrays():
             L.check(L.lib().rt_pinned_unregister(C.c_void_p(color.ctypes.data)))
             L.check(L.lib().rt_pinned_unregister(C.c_void_p(t.ctypes.data)))
         assert util.same_bits(t, c["t"]) and np.array_equal(color, c["color_normal"]), key
+
+
+def test_brute_force_path_box_cull_and_depth_bound():
+    """The <= 32-triangle kernel: looking away from the cube draws nothing, a nearer depth already in the framebuffer
+    survives, eyes inside the cube see what the reference sees (hits behind the origin included).  Against the oracle's
+    every-triangle loop, which tests/test_host_emul.py pins to the compiled reference on the same situations."""
+    a = G.scene_arrays("cube")
+    s = rt.TriangleMesh(a["vpos4"], a["indices"])          # RT_MESH_AUTO: brute force for 12 triangles
+    ps = P.Scene.mesh_brute(a["vpos4"], a["indices"])
+    W, H = 64, 40
+    pinv = rt.host_projection(W, H)[1]
+    rng = np.random.default_rng(3)
+    drew_nothing = 0
+    for radii in ((1.8, 2.5, 4.0), (1.05, 1.2), (0.2, 0.5, 0.9)):
+        for prefill in (False, True):
+            for away in (False, True):
+                for k in range(4):
+                    v = rng.normal(size=3)
+                    v /= np.linalg.norm(v)
+                    r = float(rng.choice(radii))
+                    target = 2.5 * r * v + rng.uniform(-0.5, 0.5, 3) if away else rng.uniform(-0.3, 0.3, size=3)
+                    pos, _view, vinv = rt.host_camera(eye=tuple(float(x) for x in r * v),
+                                                      target=tuple(float(x) for x in target), lock_up=bool(k % 2))
+                    t0 = (rng.choice(np.array([np.inf, 0.5, 1.2, 2.0, 2.6, 3.5], np.float32), size=(H, W)).astype(np.float32)
+                          if prefill else np.full((H, W), np.inf, np.float32))
+                    c0 = rng.integers(0, 2**32, size=(H, W), dtype=np.uint32)
+                    got = s.render(rt.make_frame(pos, vinv, pinv, W, H), color=c0, t=t0)
+                    pc, pt, _, _ = ps.render(pos, vinv, pinv, W, H, color=c0, t=t0)
+                    where = f"radii {radii} prefill {prefill} away {away} camera {k}"
+                    assert util.same_bits(got["t"], pt), where
+                    assert (got["color"] != pc).sum() <= 0.01 * W * H, where
+                    if away and radii[0] > 1.7 and not prefill:
+                        drew_nothing += int(np.isinf(got["t"]).all())
+    assert drew_nothing == 4
+    s.destroy()

@@ -67,11 +67,11 @@ def test_mesh_default_look_with_our_tree(key):
     d = util.compare_frames(r["color"], r["t"], c["color_full"], c["t_full"])
     assert d["mask_mismatch"] == 0
     print(key, "tree-dependent secondary pixels:", d["rgb_outliers"], "of", d["n_hit"])
-    if c["scene"] != "cube":
-        # leaves of a real mesh are tiny, so a secondary ray's origin is almost never inside a leaf box that holds a
-        # triangle behind it, and both trees agree; the 12-triangle cube is ALL such cases (its two reference leaves
-        # span the whole model, our brute force is one leaf): it is covered by the imported-tree test above
-        assert d["rgb_outliers"] <= 0.02 * d["n_hit"], d
+    # leaves of a real mesh are tiny, so a secondary ray's origin is almost never inside a leaf box that holds a
+    # triangle behind it, and both trees agree; on the 12-triangle cube every secondary ray starts on such a box, and
+    # the brute-force kernel's mesh-box cull + depth bound give the reference's answer there too (0 outliers when the
+    # kernel source is run on the CPU, tests/test_host_emul.py)
+    assert d["rgb_outliers"] <= 0.02 * d["n_hit"], d
 
 
 def _write_grid(path, values):

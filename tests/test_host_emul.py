@@ -62,11 +62,16 @@ def test_device_source_on_cpu_reproduces_the_golden_frames(key):
             assert (col != c[name]).sum() <= max(2, 1e-3 * W * H), f"{key}: {name} differs beyond tie pixels"
         else:
             assert np.array_equal(col, c[name]), f"{key}: {name} differs"
-    if "color_full" in c and c["color_full"] is not None and kind != "mesh":
+    if "color_full" in c and c["color_full"] is not None:
         f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=rt.SHADE_LAMBERT, shadows=True,
-                          reflections=True, plane_y=-1.0)
+                          reflections=True, plane_y=float(c["plane_y"]))
         col, t, _, _ = s.render(f)
-        assert util.same_bits(t, c["t_full"]) and np.array_equal(col, c["color_full"]), f"{key}: plane + secondary rays"
+        assert util.same_bits(t, c["t_full"]), f"{key}: plane + secondary rays, depth"
+        if kind == "mesh" and c["scene"] != "cube":
+            # a secondary ray starts on the surface: whether a triangle behind it is tested depends on the tree (T6)
+            assert (col != c["color_full"]).sum() <= 2e-3 * W * H, f"{key}: plane + secondary rays"
+        else:  # SDF scenes, and the cube's brute-force path (mesh-box cull + depth bound), are exact
+            assert np.array_equal(col, c["color_full"]), f"{key}: plane + secondary rays"
 
 
 @pytest.mark.parametrize("name,n_cams", (("example_grid", 150), ("sdf_6", 150), ("sdf_5", 100)))

@@ -452,3 +452,24 @@ def test_random_grids_vs_oracle(seed):
     for i in range(o.shape[0]):
         h, pt, pn, _ = ps.intersect(o[i], d[i])
         assert bool(hit[i]) == h and (not h or (util.same_bits(t[i], pt) and util.same_bits(nrm[i], pn))), f"seed {seed} ray {i}"
+
+
+def test_one_node_octrees_vs_oracle():
+    """A file whose root is a leaf (OctreeDev::root_inner = 0): every leaf class."""
+    W, H = 48, 32
+    pinv = rt.host_projection(W, H)[1]
+    rng = np.random.default_rng(1)
+    leaves = (np.full(8, 1000.0), np.zeros(8), rng.uniform(-0.5, 0.5, 8), rng.uniform(-0.2, 0.9, 8),
+              rng.uniform(1e-4, 2e-4, 8), np.array([0.5, 0.5, 0.5, 0.5, -0.5, -0.5, -0.5, -0.5]))
+    some_hit = False
+    for case, v in enumerate(leaves):
+        rec = np.zeros((1, 36), np.uint8)
+        rec[0, :32] = v.astype(np.float32).view(np.uint8)
+        s, ps = E.EmulScene.octree(rec), P.Scene.octree(rec)
+        for k, pos, vinv in seeded_cameras(20, seed=case):
+            col, t, _, cnt = s.render(rt.make_frame(pos, vinv, pinv, W, H))
+            pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, want_counters=True)
+            assert util.same_bits(t, pt) and np.array_equal(col, pc), f"leaf {case} camera {k}"
+            assert cnt["oct_leaf_samples"] == pcnt["octLeafSdf"]
+            some_hit |= bool(np.isfinite(t).any())
+    assert some_hit

@@ -117,14 +117,29 @@ const char *rt_last_error(void);         /* thread-local text of the last failur
 const char *rt_version(void);
 int rt_device_count(int *count);         /* number of visible CUDA devices */
 int rt_set_device(int device);           /* cudaSetDevice for the calling thread */
+/* Multi-GPU behind the reference's single call (src/main.cpp:203,206 -> Renderer::draw, src/raytracing.cpp:67-102: one
+ * call from one process renders the frame).  After rt_init(devices, n) every rt_scene_create_* builds the scene once (on
+ * devices[0]) and replicates it onto the other listed devices with device-to-device copies, and ONE rt_render_host /
+ * rt_render_device call on such a scene fans the frame out over all of them as interleaved 8-row bands:
+ *   - rt_render_host, page-locked framebuffer: every GPU stores (clear = 0: first loads) its own bands straight in the
+ *     caller's buffers over its OWN PCIe link (128-byte bulk transfers), so n GPUs bring n links to the transfer that
+ *     bounds the single-GPU call; pageable buffers: one strided copy per device, buffer and direction;
+ *   - rt_render_device, framebuffer in the HBM of one listed device: that device renders its bands on the caller's
+ *     stream, the others store theirs into it over NVLink / NVSwitch inside their render kernels (peer access is
+ *     enabled here), ordered with the caller's stream by events.  No separate gather, no NCCL.
+ * A call whose rt_frame selects bands itself (band_count > 1) runs on one device as before.  n = 0 restores the
+ * default: scenes live on the device that is current when they are created.  Call it before creating scenes. */
+int rt_init(const int *devices, int n);
+int rt_device_list(int *devices, int cap);                           /* -> number of devices of rt_init's list */
 
 /* ---- scene construction (upload once) ---------------------------------------------------------- */
 /* replaces SDFGrid + loadSDFGrid (grid_raytracing.hpp:10-22, .cpp:127-134): values[(x*sy + y)*sz + z] */
 int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t sz, int layout /*rt_grid_layout*/,
                          rt_scene **out);
 /* replaces SDFOctree + loadSDFOctree (octree_raytracing.hpp:8-49, .cpp:8-16): n x 36-byte
- * {float values[8]; uint32 childrenOffset}.  Offsets and depth are validated (a bad offset would be an
- * out-of-bounds device read). */
+ * {float values[8]; uint32 childrenOffset}.  Offsets and depth (<= 21 levels) are validated (a bad offset would be an
+ * out-of-bounds device read).  Leaves may be shared between parents; an inner node referenced by two parents (a DAG
+ * with shared subtrees, which the reference's loader would accept) is rejected with RT_ERR_INVALID, as a cycle would be. */
 int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out);
 /* replaces BVHBuilder::perform (triangles_raytracing.hpp:40, .cpp:227-258): builds our own 8-wide BVH on the
  * host and uploads it with the leaf triangles pre-gathered.  vpos4 = SimpleMesh::vPos4f (x,y,z,w),
@@ -144,7 +159,8 @@ int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tr
 int rt_scene_build_ms(const rt_scene *scene, float *device_ms);
 void rt_scene_destroy(rt_scene *scene);
 int rt_scene_kind_of(const rt_scene *scene);             /* rt_scene_kind */
-int rt_scene_device(const rt_scene *scene);
+int rt_scene_device(const rt_scene *scene);               /* the device the scene was built on (replica 0) */
+int rt_scene_replicas(const rt_scene *scene, int *devices, int cap); /* -> number of devices holding the scene */
 /* bytes of scene data resident in HBM, and the model's bounding box (meshes: calc_bbox, raytracing.hpp:22-37;
  * SDF scenes: [-1,1]^3) */
 int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]);
@@ -165,13 +181,15 @@ int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *col
  * (/ prim) out.  Returns the device time of the render kernels alone in *device_ms (the reference returns
  * its own stopwatch, raytracing.cpp:97-101) and of the whole call incl. copies in *total_ms.  Any of prim,
  * device_ms, total_ms, counters may be NULL.
- * Page-locked framebuffer: when color and t_inout are pinned host memory (rt_pinned_alloc / rt_pinned_register below, or
- * any cudaHostAlloc / cudaHostRegister memory), the whole frame is rendered (band_count <= 1), W % 8 == 0, prim /
- * counters are NULL and no secondary rays are asked for, the kernel works on the caller's buffers directly over PCIe:
- * with rt_frame.clear = 1 it stores its tiles as 128-byte bulk stores; with clear = 0 (the reference's in/out
- * framebuffer) it first fetches each tile's previous colour and depth with bulk loads and stores the merged tile back.
- * No device framebuffer, no copy engine; *device_ms then equals *total_ms.  Pageable buffers and every other
- * combination go through the pipelined copies. */
+ * Page-locked framebuffer: when color and t_inout (and prim, if given) are pinned host memory (rt_pinned_alloc /
+ * rt_pinned_register below, or any cudaHostAlloc / cudaHostRegister memory) covering all W*H*4 bytes of each buffer and
+ * 16-byte aligned (anything else silently takes the copies), W % 8 == 0 (band_rows % 4 == 0 for a banded call) and
+ * counters is NULL, the kernel works on the caller's buffers directly over PCIe, for every scene kind and shading mode
+ * (secondary rays and the ground plane included): with rt_frame.clear = 1 it stores its tiles as 128-byte bulk stores;
+ * with clear = 0 (the reference's in/out framebuffer) it first fetches each tile's previous contents with bulk loads and
+ * stores the merged tile back.  No device framebuffer, no copy engine; *device_ms then equals *total_ms.  Pageable
+ * buffers and workload counters go through the pipelined copies.  On a scene replicated by rt_init every listed GPU
+ * does this for its own bands over its own PCIe link. */
 int rt_render_host(const rt_scene *scene, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
                    float *device_ms, float *total_ms, rt_counters *counters);
 

@@ -456,31 +456,40 @@ static BvhHit bvh_node(const PortScene *s, uint32_t index, v3 o, v3 d, float tNe
 
 /* No BVH given: every triangle in index order, first closest wins (the loop ray_pack.ispc:167-202 describes,
  * with the leaf acceptance rule of triangles_raytracing.cpp:324-331: no t-range test on the triangle itself).
- * Tree-independent truth for meshes whose reference-built BVH is not at hand (the GPU box). nIdx is passed in
- * nBvhNodes' place.  The one thing a tree adds to the answer is box culling against [tNear, tFar]
- * (triangles_raytracing.cpp:266-297): a hit beyond tFar (the depth already in the framebuffer) lies in leaf boxes that
- * start beyond tFar and is never reached, while hits before tNear or behind the origin are (their boxes straddle the
- * origin).  Two tree-independent conditions restate that: the ray must pass intersect_box_8's test (slab_lane) on the
- * mesh's bounding box, inside which every box of any tree lies (a ray looking away from the mesh, or stopped by tFar
- * in front of it, reaches no leaf), and `th <= tFar`.  Checked against the compiled reference on the cube: frames from
- * outside and inside, looking at and away from it, cleared and pre-filled depth buffers, and single rays with
- * arbitrary ranges (tests/test_oracle_port.py, tests/test_host_emul.py). */
+ * nIdx / 3 is passed in bvhNodeBytes' place.
+ *
+ * <= 8 triangles: this IS the reference.  BVHBuilder::createNode (triangles_raytracing.cpp:155-186) finds no split
+ * for a range of <= 24 indices (tryDivide returns at :120-122) and makes node 0 a leaf; traverseNode(0) on a leaf
+ * (:292-331) tests its triangles in index order with no box test and no range check whatsoever, so hits behind the
+ * origin, in front of tNear and beyond tFar are all returned.  Pinned bit for bit against the compiled reference on a
+ * 2-triangle quad, a tetrahedron and an open 5-triangle fan from outside, grazing and inside, looking at and away,
+ * cleared and pre-filled depth, with and without plane + secondary rays (tests/test_small_meshes.py).
+ *
+ * > 8 triangles: the reference reaches triangles only through child boxes that pass intersect_box_8 against
+ * [tNear, tFar] (:271-291), and which triangles share a box is a property of ITS tree.  This loop is then the
+ * TREE-INDEPENDENT truth only: it equals the reference wherever the closest hit does not depend on the tree (eye outside
+ * the mesh, cleared framebuffer: every benchmark configuration; pinned on 4 meshes x 94 cameras).  Two tree-independent
+ * conditions stand in for the box culling elsewhere: the ray must pass the same slab test on the mesh's bounding box
+ * (inside which every box of any tree lies), and `th <= tFar`.  On cube.obj that also reproduces the reference from
+ * inside and with pre-filled depth (tests/test_host_emul.py); on other meshes those views are tree-dependent and only
+ * the reference's own tree (bvh_node above, rt_scene_create_mesh_bvh8 in the product) answers them. */
 static BvhHit mesh_brute(const PortScene *s, v3 o, v3 d, float tNear, float tFar, PortCounters *cnt) {
   BvhHit result = {0, INFINITY, 0};
-  {
+  uint32_t nTri = s->bvhNodeBytes; /* triangle count when bvhNodes == NULL */
+  const int rootLeaf = nTri <= 8;
+  if (!rootLeaf) {
     v3 inv = {1.0f / d.x, 1.0f / d.y, 1.0f / d.z};
     if (slab_lane(s->bboxMin[0], s->bboxMin[1], s->bboxMin[2], s->bboxMax[0], s->bboxMax[1], s->bboxMax[2], o, inv, tNear,
                   tFar) < 0.0f)
       return result;
   }
-  uint32_t nTri = s->bvhNodeBytes; /* triangle count when bvhNodes == NULL */
   for (uint32_t k = 0; k < nTri; ++k) {
     if (cnt) cnt->bvhTris++;
     v3 v0 = mesh_vertex(s, s->indices[3 * k]);
     v3 v1 = mesh_vertex(s, s->indices[3 * k + 1]);
     v3 v2 = mesh_vertex(s, s->indices[3 * k + 2]);
     float th;
-    if (tri_lane(o, d, v0, v1, v2, &th) && th <= tFar && (!result.hitten || result.t > th)) {
+    if (tri_lane(o, d, v0, v1, v2, &th) && (rootLeaf || th <= tFar) && (!result.hitten || result.t > th)) {
       result.hitten = 1;
       result.t = th;
       result.tri = k;

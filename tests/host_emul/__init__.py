@@ -106,9 +106,12 @@ class EmulScene:
     def mesh(vpos4, indices, brute=None) -> "EmulScene":
         v = np.ascontiguousarray(vpos4, np.float32).reshape(-1, 4)
         i = np.ascontiguousarray(indices, np.uint32).reshape(-1)
-        if brute is None:
-            brute = i.size // 3 <= 32  # rt_scene_create_mesh's RT_MESH_AUTO rule
-        return EmulScene(lib().emul_mesh(_p(v), v.shape[0], _p(i), i.size, int(bool(brute))))
+        # rt_scene_create_mesh's rules: <= 8 triangles are the reference's one-leaf tree (BRUTE_ROOT_LEAF = 2) unless a
+        # tree is asked for; RT_MESH_AUTO (brute=None) builds a tree beyond that; RT_MESH_BRUTE (brute=True) is
+        # BRUTE_BOXED = 1 there
+        n_tri = i.size // 3
+        mode = 0 if brute is False else 2 if n_tri <= 8 else 1 if brute else 0
+        return EmulScene(lib().emul_mesh(_p(v), v.shape[0], _p(i), i.size, mode))
 
     @staticmethod
     def mesh_refbvh(vpos4, indices_bvh, nodes, prim_of_permuted=None) -> "EmulScene":

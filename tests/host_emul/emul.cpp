@@ -168,10 +168,10 @@ EmulScene *emul_octree(const void *nodes36, uint32_t n) {
   return e;
 }
 
-// brute != 0: the <= 32-triangle path (every triangle, no tree); else the product's host-built BVH8
+// brute = BRUTE_NONE / BRUTE_BOXED / BRUTE_ROOT_LEAF (rt_scene.h): the product's host-built BVH8 or the no-tree paths
 EmulScene *emul_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, int brute) {
   auto *e = new EmulScene;
-  if (!build_bvh8(vpos4, n_verts, indices, n_indices, brute != 0, e->bvh, e->err)) {
+  if (!build_bvh8(vpos4, n_verts, indices, n_indices, (uint32_t)brute, e->bvh, e->err)) {
     delete e;
     return nullptr;
   }
@@ -181,7 +181,7 @@ EmulScene *emul_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *indic
   m.tris = e->bvh.tris.data();
   m.n_nodes = (uint32_t)e->bvh.nodes.size();
   m.n_tris = (uint32_t)e->bvh.tris.size();
-  m.brute = brute ? 1u : 0u;
+  m.brute = e->bvh.brute;
   m.literal_order = 0u;
   return e;
 }
@@ -201,7 +201,7 @@ EmulScene *emul_mesh_refbvh(const float *vpos4, uint32_t n_verts, const uint32_t
   m.tris = e->bvh.tris.data();
   m.n_nodes = (uint32_t)e->bvh.nodes.size();
   m.n_tris = (uint32_t)e->bvh.tris.size();
-  m.brute = 0u;
+  m.brute = e->bvh.brute;  // a one-leaf reference tree becomes the BRUTE_ROOT_LEAF scene
   m.literal_order = 1u;
   return e;
 }

@@ -57,21 +57,29 @@ def test_mesh_default_look_with_the_reference_tree_is_bit_exact():
         assert np.array_equal(r["color"], c["color_shadow"])
 
 
+# colour pixels of the default look that differ from the reference's frame with OUR tree, counted by running the same
+# kernel source on the CPU (tests/host_emul): secondary rays start on the surface, triangle hits are not range-checked
+# (SURVEY T6), so a handful of shadow / reflection outcomes depend on the reference's own tree
+TREE_DEPENDENT_PIXELS = {"cube|default|128x128": 0, "stanford-bunny|default|160x90": 3, "stanford-bunny|orbit5|96x64": 1,
+                         "as1-oc-214|default|96x64": 1}
+
+
 @pytest.mark.parametrize("key", [c for c in FULL if c.split("|")[0] in util.MESHES])
 def test_mesh_default_look_with_our_tree(key):
     """With our own tree primary visibility (depth) is still bit-exact; shading may differ where a secondary ray's
-    outcome is tree-dependent in the reference itself. Those pixels are counted and bounded."""
+    outcome is tree-dependent in the reference itself.  Those pixels are counted and must be the ones the CPU run of the
+    same source found (cube: none, with the tree and with the explicit brute-force rule)."""
     c = G.case(key)
-    r = util.cuda_scene(G, c["scene"]).render(_full_frame(c))
-    assert util.same_bits(r["t"], c["t_full"]), key
-    d = util.compare_frames(r["color"], r["t"], c["color_full"], c["t_full"])
-    assert d["mask_mismatch"] == 0
-    print(key, "tree-dependent secondary pixels:", d["rgb_outliers"], "of", d["n_hit"])
-    # leaves of a real mesh are tiny, so a secondary ray's origin is almost never inside a leaf box that holds a
-    # triangle behind it, and both trees agree; on the 12-triangle cube every secondary ray starts on such a box, and
-    # the brute-force kernel's mesh-box cull + depth bound give the reference's answer there too (0 outliers when the
-    # kernel source is run on the CPU, tests/test_host_emul.py)
-    assert d["rgb_outliers"] <= 0.02 * d["n_hit"], d
+    a = G.scene_arrays(c["scene"])
+    accels = (rt.MESH_AUTO, rt.MESH_BRUTE) if c["scene"] == "cube" else (rt.MESH_AUTO,)
+    for accel in accels:
+        r = rt.TriangleMesh(a["vpos4"], a["indices"], accel=accel).render(_full_frame(c))
+        assert util.same_bits(r["t"], c["t_full"]), key
+        d = util.compare_frames(r["color"], r["t"], c["color_full"], c["t_full"])
+        assert d["mask_mismatch"] == 0
+        differ = int((r["color"] != c["color_full"]).sum())
+        print(key, "accel", accel, "tree-dependent secondary pixels:", differ, "of", d["n_hit"])
+        assert differ <= TREE_DEPENDENT_PIXELS[key], (key, accel, differ, d)
 
 
 def _write_grid(path, values):

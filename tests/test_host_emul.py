@@ -243,8 +243,9 @@ def _ray_batch(seed, n_random=1500):
 
 @pytest.mark.parametrize("name", ("example_grid", "sdf_6", "sdf_5", "cube"))
 def test_device_source_on_cpu_single_rays_vs_oracle(name):
-    """IScene::intersect (rays_kernel's body): hit flag, t and normal bit for bit, axis-parallel rays included."""
-    s, kind = emul_scene(name)
+    """IScene::intersect (rays_kernel's body): hit flag, t and normal bit for bit, axis-parallel rays included.
+    (cube: rays that start inside a mesh are tree-dependent; the explicit RT_MESH_BRUTE rule is the oracle loop's.)"""
+    s, kind = emul_scene(name, **({"brute": True} if name == "cube" else {}))
     ps = util.port_scene(G, name)
     o, d = _ray_batch(seed=len(name))
     for t_near, t_far, plane in ((0.01, 100.0, None), (0.3, 2.2, None), (0.01, 100.0, -1.0)):

@@ -83,7 +83,7 @@ def _cam(W, H):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,W,H", (("example_grid_x4", 3840, 2160), ("example_grid_x8", 3840, 2160),
-                                      ("octree_d8", 3840, 2160), ("octree_d9", 1920, 1080)))
+                                      ("octree_d8", 3840, 2160), ("octree_d9", 3840, 2160)))
 def test_large_sdf_standins_bit_exact_at_full_size(name, W, H):
     """BASELINE.json configs[2], [3]: the large grid / octree stand-ins at 3840x2160 against the plain-C oracle."""
     import triangles_sdf_cpu_raytracing_b200 as rt
@@ -123,7 +123,7 @@ def test_large_mesh_standin_orbit_vs_reference():
     c = _cam(W, H)
     ref = R.RefOracle().mesh(a["vpos4"], a["indices"])
     s = rt.TriangleMesh(a["vpos4"], a["indices"])
-    for k in (0, 17, 40):  # frames of the 64-frame orbit
+    for k in (0, 8, 17, 24, 32, 40, 48, 56, 63):  # frames of the 64-frame orbit
         pos, _view, vinv = rt.host_camera(n_rotate=k, dx=ORBIT_DX, dy=0.0)
         want_c, want_t, _ = ref.render(R.CamSpec(n_rotate=k, dx=ORBIT_DX, dy=0.0), W, H, proj_inv=c["projInv"])
         r = s.render(rt.make_frame(pos, vinv, c["projInv"], W, H), want_prim=True)
@@ -140,3 +140,40 @@ def test_large_mesh_standin_orbit_vs_reference():
             hit, tt, _ = P.triangle(pos, d, tri.astype(np.float32))
             assert hit and util.same_bits(tt, want_t[row, x]), f"orbit frame {k} pixel ({x},{row}) is not a tie"
     s.destroy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,key,W,H", (("cube", "cube|default|128x128", 512, 512),
+                                          ("example_grid", "example_grid|default|160x90", 1920, 1080)))
+def test_baseline_configs_0_and_1_at_their_own_size(name, key, W, H):
+    """BASELINE.json configs[0] (cube.obj 512x512) and configs[1] (example_grid.grid 1920x1080) at exactly those sizes:
+    against the reference's own Renderer::draw where oracle/_ref travelled to the box, and against the plain-C oracle."""
+    import triangles_sdf_cpu_raytracing_b200 as rt
+    from oracle import ref_oracle as R
+    rt.set_math_mode(rt.MATH_EXACT)
+    rt.set_sched_mode(rt.SCHED_AUTO)
+    c = G.case(key)
+    assert abs(W / H - c["W"] / c["H"]) < 1e-6
+    a = G.scene_arrays(name)
+    wants = []
+    pc, pt, _, _ = util.port_scene(G, name).render(c["rayPos"], c["viewInv"], c["projInv"], W, H)
+    wants.append(("oracle/port_oracle.c", pc, pt))
+    if R.available():
+        o = R.RefOracle()
+        ref = o.mesh(a["vpos4"], a["indices"]) if "vpos4" in a else o.grid(a["values"])
+        rc, rtt, _ = ref.render(R.CamSpec(), W, H, proj_inv=c["projInv"])
+        wants.append(("oracle/_ref", rc, rtt))
+    accels = (rt.MESH_AUTO, rt.MESH_BRUTE, rt.MESH_BVH8) if name == "cube" else (None,)
+    for accel in accels:
+        s = util.cuda_scene(G, name, **({"accel": accel} if accel is not None else {}))
+        r = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H))
+        rp = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True),
+                      color=np.full((H, W), 0x5A5A5A5A, np.uint32), t=np.full((H, W), 0.25, np.float32))
+        for who, wc, wt in wants:
+            assert util.same_bits(r["t"], wt), f"{name} {W}x{H} accel {accel}: depth differs from {who}"
+            assert util.same_bits(rp["t"], wt), f"{name} {W}x{H} accel {accel}, fused clear: depth differs from {who}"
+            if name == "cube":  # the two triangles of a face tie exactly along their shared diagonal: same normal
+                assert np.array_equal(r["color"], wc) and np.array_equal(rp["color"], wc), (who, accel)
+            else:
+                assert np.array_equal(r["color"], wc) and np.array_equal(rp["color"], wc), who
+        s.destroy()

@@ -6,4 +6,4 @@ from ._lib import (GRID_AUTO, GRID_BRICKS, GRID_LINEAR, LIB_PATH, MATH_EXACT, MA
                    MESH_BVH8, MESH_LBVH_GPU, PRIM_MISS, PRIM_PLANE, SCHED_AUTO, SCHED_COMPACT, SCHED_PERSISTENT, SCHED_TILES, SHADE_COLOR,
                    SHADE_LAMBERT, SHADE_NORMAL, RtCounters, RtError, RtFrame, lib)
 from .api import (PinnedFrameBuffer, host_camera, host_load_obj, host_projection, Scene, SDFGrid, SDFOctree, TriangleMesh, TriangleMeshFromReferenceBVH, load_grid_file,
-                  load_octree_file, make_frame, set_math_mode, set_sched_mode)
+                  init, load_octree_file, make_frame, set_math_mode, set_sched_mode)

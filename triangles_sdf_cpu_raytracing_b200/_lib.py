@@ -46,6 +46,9 @@ SIGNATURES = {
     "rt_version": (C.c_char_p, []),
     "rt_device_count": (_i, [C.POINTER(_i)]),
     "rt_set_device": (_i, [_i]),
+    "rt_init": (_i, [_vp, _i]),
+    "rt_device_list": (_i, [_vp, _i]),
+    "rt_scene_replicas": (_i, [_vp, _vp, _i]),
     "rt_scene_create_grid": (_i, [_vp, _u32, _u32, _u32, _i, _pp]),
     "rt_scene_create_octree": (_i, [_vp, _u32, _pp]),
     "rt_scene_create_mesh": (_i, [_vp, _u32, _vp, _u32, _i, _pp]),

@@ -102,6 +102,12 @@ class Scene:
         L.check(L.lib().rt_scene_info(self._h, C.byref(b), lo, hi))
         return dict(device_bytes=int(b.value), bbox_min=np.array(lo[:], np.float32), bbox_max=np.array(hi[:], np.float32))
 
+    def replicas(self):
+        """Devices that hold a copy of the scene (rt_init)."""
+        d = np.zeros(64, np.int32)
+        n = L.lib().rt_scene_replicas(self._h, _ptr(d), 64)
+        return [int(x) for x in d[:n]]
+
     def build_ms(self) -> float:
         """Device time of the on-device part of scene construction (octree ingestion, device BVH build)."""
         ms = C.c_float()
@@ -219,6 +225,13 @@ def load_octree_file(path: str) -> np.ndarray:
     if raw.size != 4 + 36 * n:
         raise ValueError(f"{path}: size does not match its node count {n}")
     return raw[4:].reshape(n, 36)
+
+
+def init(devices=None):
+    """rt_init: scenes created afterwards are replicated on every listed device and ONE render call fans the frame out
+    over them (include/rt_b200.h).  None / [] restores single-device scenes on the current device."""
+    d = np.ascontiguousarray(list(devices or []), np.int32)
+    L.check(L.lib().rt_init(_ptr(d) if d.size else None, int(d.size)))
 
 
 def set_math_mode(mode: int):

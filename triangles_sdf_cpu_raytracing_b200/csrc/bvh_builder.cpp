@@ -218,7 +218,7 @@ TriDev make_tri(const float v[3][3], uint32_t prim) {
 
 }  // namespace
 
-bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, bool brute,
+bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, uint32_t brute,
                 HostBvh &out, std::string &err) {
   if (!vpos4 || !indices || n_indices == 0 || n_indices % 3 != 0) {
     err = "mesh needs a non-empty index list with 3 indices per triangle";
@@ -249,10 +249,15 @@ bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, u
   }
   out.nodes.clear();
   out.stack_need = 0;
-  if (brute) {
-    out.tris = std::move(all);  // original order: ties keep the lowest prim id
-    // one node whose lane 0 is the mesh's bounding box: the brute-force kernel culls a ray against it the way the
-    // reference culls against its child boxes (every one of them lies inside this box)
+  out.brute = brute;
+  if (brute != BRUTE_NONE) {
+    if (brute == BRUTE_ROOT_LEAF && nTri > ROOT_LEAF_MAX_TRIS) {
+      err = "root-leaf meshes hold at most 8 triangles";
+      return false;
+    }
+    out.tris = std::move(all);  // original order: ties keep the lowest prim id (the reference's leaf order, :324-331)
+    // one node whose lane 0 is the mesh's bounding box: BRUTE_BOXED culls a ray against it the way the reference culls
+    // against its child boxes (every one of them lies inside this box); BRUTE_ROOT_LEAF never looks at it
     BvhNode root{};
     for (int l = 0; l < 8; ++l) root.child[l] = BVH_EMPTY;
     for (int a = 0; a < 3; ++a) {
@@ -320,17 +325,23 @@ bool import_reference_bvh(const float *vpos4, uint32_t n_verts, const uint32_t *
   std::vector<int64_t> newIndex(n_nodes, -1);
   std::vector<uint32_t> order;
   out.nodes.clear();
+  out.brute = BRUTE_NONE;
   if (is_leaf(0)) {
-    out.nodes.emplace_back();
-    clear_node(out.nodes[0]);
-    uint32_t w;
-    if (!leaf_ref(0, w)) {
+    // The reference's whole tree is one leaf (<= 8 triangles): traverseNode(0) tests its triangles with no box test
+    // and no range check (triangles_raytracing.cpp:292-331).  That is the BRUTE_ROOT_LEAF scene, on the leaf's range.
+    const uint32_t start = u32_at(0, 0), count = u32_at(0, 4);
+    if (start % 3 || count % 3 || count == 0 || count > 24 || (uint64_t)start + count > n_indices) {
       err = "reference BVH: bad leaf record";
       return false;
     }
+    std::vector<TriDev> leafTris(out.tris.begin() + start / 3, out.tris.begin() + (start + count) / 3);
+    out.tris = std::move(leafTris);
+    out.nodes.emplace_back();
+    clear_node(out.nodes[0]);
     set_child_box(out.nodes[0], 0, total);
-    out.nodes[0].child[0] = w;
-    out.stack_need = 1;
+    out.nodes[0].child[0] = BVH_LEAF_BIT;
+    out.stack_need = 0;
+    out.brute = BRUTE_ROOT_LEAF;
     return true;
   }
   newIndex[0] = 0;

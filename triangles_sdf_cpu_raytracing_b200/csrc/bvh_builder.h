@@ -16,11 +16,13 @@ struct HostBvh {
   std::vector<TriDev> tris;    // leaf triangles in tree order, prim id in v0.w
   float bbox_min[3], bbox_max[3];
   int stack_need = 0;          // worst-case traversal stack entries
+  uint32_t brute = BRUTE_NONE; // BRUTE_*: no tree, `tris` in the original order (rt_scene.h)
 };
 
 // vpos4: n_verts x (x,y,z,w); indices: 3 per triangle. Triangles are divided by w exactly as
 // triangles_raytracing.cpp:307-309 does per visit.  Returns false and sets err on bad input.
-bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, bool brute,
+// brute = BRUTE_NONE builds the tree; BRUTE_BOXED / BRUTE_ROOT_LEAF only pack the triangles.
+bool build_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices, uint32_t n_indices, uint32_t brute,
                 HostBvh &out, std::string &err);
 
 // nodes: n_nodes images of the reference's BVH8Node (triangles_raytracing.hpp:10-36): Box8 (192 B) | realCount u32 |

@@ -6,7 +6,7 @@
 //                           octree_raytracing.cpp:132-135); records are staged through shared memory so both the
 //                           4-byte-aligned reads and the 16-byte writes are coalesced
 //           k_oct_frontier  validation as a level-synchronous walk from the root: every inner node's 8 children in
-//                           range, every node reached at most once (a tree: no sharing, no cycles), depth bounded.
+//                           range, every INNER node reached at most once (no cycles; leaves may be shared), depth bounded.
 //                           A bad childrenOffset would otherwise be an out-of-bounds device read in the render kernel.
 //   grid    k_grid_bricks   linear x-major/z-fastest samples -> 8x8x8-sample bricks (rt_scene.h), one thread per
 //                           output sample, coalesced writes
@@ -68,11 +68,15 @@ __global__ void k_oct_frontier(const uint32_t *rawLink, uint32_t n, const uint32
   }
   for (uint32_t c = 0; c < 8u; ++c) {
     const uint32_t child = off + c;
+    // Leaves may be shared between parents (files with de-duplicated empty leaves load and render in the reference,
+    // octree_raytracing.cpp:8-16,166-202): a leaf has no box of its own and ends the descent, so sharing one is harmless.
+    // An INNER node reached twice is rejected: it is how a cycle would look, and the depth bound below is per node.
+    if (rawLink[child] == 0u) continue;
     if (atomicExch(&seen[child], 1u) != 0u) {
       atomicMax(&st->error, 2u);
       continue;
     }
-    if (rawLink[child] != 0u) frontOut[atomicAdd(&st->count[outSlot], 1u)] = child;
+    frontOut[atomicAdd(&st->count[outSlot], 1u)] = child;
   }
 }
 
@@ -172,7 +176,7 @@ int ingest_octree_device(const void *nodes36, uint32_t n, uint32_t **linkOut, fl
     ce = cudaMemcpy(&h, st, sizeof h, cudaMemcpyDeviceToHost);  // also the level's sync point
     if (ce != cudaSuccess) break;
     if (h.error == 1u) return bail(INGEST_INVALID, "octree childrenOffset out of range");
-    if (h.error == 2u) return bail(INGEST_INVALID, "octree node referenced twice (not a tree)");
+    if (h.error == 2u) return bail(INGEST_INVALID, "octree inner node referenced twice (shared subtrees / cycles are not supported; shared leaves are)");
     ++depth;  // the children of this frontier exist: the tree reaches level `depth`
     nIn = h.count[cur ^ 1];
     const uint32_t zero = 0;

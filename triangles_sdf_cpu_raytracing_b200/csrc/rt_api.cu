@@ -5,7 +5,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -65,20 +67,18 @@ constexpr int N_TILE_COUNTERS = 64;
 
 }  // namespace
 
-struct rt_scene {
-  int kind = -1;
+// The scene on ONE device.  A scene created after rt_init(devs, n) has one replica per listed device (scene data is
+// read-only and small next to 180 GB of HBM: replicated, never sharded); otherwise a single replica on the device
+// that was current at creation.
+struct Replica {
   int device = 0;
   int sm_count = 148;
   SceneDev dev{};
-  std::vector<void *> allocs;
-  uint64_t bytes = 0;
-  float bbox_min[3] = {-1, -1, -1}, bbox_max[3] = {1, 1, 1};
-  float build_ms = 0.0f;              // device time of an on-device BVH build
-  uint32_t *tile_counters = nullptr;  // ring, one per in-flight persistent launch
+  std::vector<std::pair<void *, size_t>> allocs;  // device allocations and their sizes (cloned onto the other devices)
+  uint32_t *tile_counters = nullptr;              // ring, one per in-flight persistent launch
   std::atomic<uint32_t> next_counter{0};
-  // framebuffer cache of rt_render_host
-  std::mutex host_mu;
-  uint32_t *h_color = nullptr;
+  // per-device state of rt_render_host / of a fanned-out rt_render_device
+  uint32_t *h_color = nullptr;  // device framebuffer of the copy pipeline (allocated on first use)
   float *h_t = nullptr;
   uint32_t *h_prim = nullptr;
   rt_counters *h_cnt = nullptr;
@@ -86,67 +86,138 @@ struct rt_scene {
   cudaStream_t h_stream = nullptr, h_up = nullptr, h_down = nullptr;  // kernels, H2D copies, D2H copies
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_up[16] = {}, ev_k[16] = {};  // per row chunk: upload done, kernel done
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // fan-out of one frame over the replicas (no timing)
+};
+
+struct rt_scene {
+  int kind = -1;
+  std::vector<std::unique_ptr<Replica>> reps;  // reps[0] is where the scene was built
+  uint64_t bytes = 0;
+  float bbox_min[3] = {-1, -1, -1}, bbox_max[3] = {1, 1, 1};
+  float build_ms = 0.0f;  // device time of an on-device BVH build / octree ingestion
+  std::mutex host_mu;     // rt_render_host is serialised per scene (it owns the replicas' streams and buffers)
 };
 
 namespace {
+
+// rt_init's device list (empty: scenes live on the device current at their creation)
+std::mutex g_dev_mu;
+std::vector<int> g_devs;
 
 int scene_begin(rt_scene **out, rt_scene *&s) {
   if (!out) return fail(RT_ERR_INVALID, "out pointer is null");
   *out = nullptr;
   int dev = 0;
-  RT_CUDA(cudaGetDevice(&dev));
-  s = new rt_scene;
-  s->device = dev;
+  {
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    if (!g_devs.empty()) dev = g_devs[0];
+    else RT_CUDA(cudaGetDevice(&dev));
+  }
   cudaDeviceProp p;
   cudaError_t e = cudaGetDeviceProperties(&p, dev);
-  if (e != cudaSuccess) {
-    delete s;
-    return cuda_fail(e, "cudaGetDeviceProperties");
-  }
-  s->sm_count = p.multiProcessorCount;
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceProperties");
+  s = new rt_scene;
+  s->reps.emplace_back(new Replica);
+  s->reps[0]->device = dev;
+  s->reps[0]->sm_count = p.multiProcessorCount;
   return RT_OK;
 }
 
+// cudaMalloc + copy on the CURRENT device (the creating entry point holds a DeviceGuard on reps[0]->device)
 template <class T>
 int upload(rt_scene *s, const T *host, size_t n, const T **devOut) {
   void *d = nullptr;
   size_t bytes = std::max<size_t>(n * sizeof(T), 16);
   RT_CUDA(cudaMalloc(&d, bytes));
-  s->allocs.push_back(d);
+  s->reps[0]->allocs.emplace_back(d, bytes);
   s->bytes += n * sizeof(T);
   if (n) RT_CUDA(cudaMemcpy(d, host, n * sizeof(T), cudaMemcpyHostToDevice));
   *devOut = static_cast<const T *>(d);
   return RT_OK;
 }
 
-int scene_finish(rt_scene *s, rt_scene **out) {
+void adopt(rt_scene *s, void *d, size_t bytes) { s->reps[0]->allocs.emplace_back(d, std::max<size_t>(bytes, 16)); }
+
+int finish_replica(Replica &r) {
   void *d = nullptr;
   RT_CUDA(cudaMalloc(&d, N_TILE_COUNTERS * sizeof(uint32_t)));
-  s->allocs.push_back(d);
-  s->tile_counters = static_cast<uint32_t *>(d);
+  r.allocs.emplace_back(d, N_TILE_COUNTERS * sizeof(uint32_t));
+  r.tile_counters = static_cast<uint32_t *>(d);
   RT_CUDA(cudaMemset(d, 0, N_TILE_COUNTERS * sizeof(uint32_t)));
   RT_CUDA(cudaDeviceSynchronize());
+  return RT_OK;
+}
+
+// the device copy of `src` (an allocation of `from`) on the current device
+template <class T>
+int clone_ptr(const Replica &from, Replica &to, const T *&field) {
+  if (!field) return RT_OK;
+  for (const auto &a : from.allocs)
+    if (a.first == static_cast<const void *>(field)) {
+      void *d = nullptr;
+      RT_CUDA(cudaMalloc(&d, a.second));
+      to.allocs.emplace_back(d, a.second);
+      RT_CUDA(cudaMemcpyPeer(d, to.device, a.first, from.device, a.second));
+      field = static_cast<const T *>(d);
+      return RT_OK;
+    }
+  return fail(RT_ERR_CUDA, "internal: scene pointer without an allocation record");
+}
+
+// Builds the remaining replicas (rt_init's devices 1..n-1) from reps[0] with device-to-device copies: the host data is
+// parsed, validated and laid out once, whatever built it (host BVH, device LBVH, device octree ingestion).
+int scene_finish(rt_scene *s, rt_scene **out) {
+  int rc = finish_replica(*s->reps[0]);
+  if (rc) return rc;
+  std::vector<int> devs;
+  {
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    devs = g_devs;
+  }
+  for (size_t j = 1; j < devs.size(); ++j) {
+    DeviceGuard g(devs[j]);
+    if (!g.ok) return fail(RT_ERR_CUDA, "cannot select a device of rt_init's list");
+    cudaDeviceProp p;
+    RT_CUDA(cudaGetDeviceProperties(&p, devs[j]));
+    s->reps.emplace_back(new Replica);
+    Replica &r = *s->reps.back(), &r0 = *s->reps[0];
+    r.device = devs[j];
+    r.sm_count = p.multiProcessorCount;
+    r.dev = r0.dev;
+    if ((rc = clone_ptr(r0, r, r.dev.grid.values))) return rc;
+    if ((rc = clone_ptr(r0, r, r.dev.oct.link))) return rc;
+    if ((rc = clone_ptr(r0, r, r.dev.oct.values))) return rc;
+    if ((rc = clone_ptr(r0, r, r.dev.mesh.nodes))) return rc;
+    if ((rc = clone_ptr(r0, r, r.dev.mesh.tris))) return rc;
+    if ((rc = finish_replica(r))) return rc;
+  }
   *out = s;
   return RT_OK;
 }
 
+void replica_free(Replica &r) {
+  DeviceGuard g(r.device);
+  for (auto &a : r.allocs) cudaFree(a.first);
+  if (r.h_color) cudaFree(r.h_color);
+  if (r.h_t) cudaFree(r.h_t);
+  if (r.h_prim) cudaFree(r.h_prim);
+  if (r.h_cnt) cudaFree(r.h_cnt);
+  for (auto &e : r.ev)
+    if (e) cudaEventDestroy(e);
+  for (auto &e : r.ev_up)
+    if (e) cudaEventDestroy(e);
+  for (auto &e : r.ev_k)
+    if (e) cudaEventDestroy(e);
+  if (r.ev_fork) cudaEventDestroy(r.ev_fork);
+  if (r.ev_join) cudaEventDestroy(r.ev_join);
+  if (r.h_stream) cudaStreamDestroy(r.h_stream);
+  if (r.h_up) cudaStreamDestroy(r.h_up);
+  if (r.h_down) cudaStreamDestroy(r.h_down);
+}
+
 void scene_free(rt_scene *s) {
   if (!s) return;
-  DeviceGuard g(s->device);
-  for (void *p : s->allocs) cudaFree(p);
-  if (s->h_color) cudaFree(s->h_color);
-  if (s->h_t) cudaFree(s->h_t);
-  if (s->h_prim) cudaFree(s->h_prim);
-  if (s->h_cnt) cudaFree(s->h_cnt);
-  for (auto &e : s->ev)
-    if (e) cudaEventDestroy(e);
-  for (auto &e : s->ev_up)
-    if (e) cudaEventDestroy(e);
-  for (auto &e : s->ev_k)
-    if (e) cudaEventDestroy(e);
-  if (s->h_stream) cudaStreamDestroy(s->h_stream);
-  if (s->h_up) cudaStreamDestroy(s->h_up);
-  if (s->h_down) cudaStreamDestroy(s->h_down);
+  for (auto &r : s->reps) replica_free(*r);
   delete s;
 }
 
@@ -187,15 +258,18 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   // SDFGrid::sdf maps [-1,1] to [0,size-1] (grid_raytracing.cpp:8-11): every axis needs two samples
   if (sx < 2 || sy < 2 || sz < 2) return fail(RT_ERR_INVALID, "grid needs at least 2 samples per axis");
   // element offsets are 32-bit on the device, also for the brick-padded copy
-  if ((uint64_t)((sx + 7) & ~7u) * ((sy + 7) & ~7u) * ((sz + 7) & ~7u) >= (1ull << 32))
+  const uint64_t px = ((uint64_t)sx + 7) & ~7ull, py = ((uint64_t)sy + 7) & ~7ull, pz = ((uint64_t)sz + 7) & ~7ull;
+  if (px >= (1ull << 32) || py >= (1ull << 32) || pz >= (1ull << 32) || px * py >= (1ull << 32) ||
+      px * py * pz >= (1ull << 32))
     return fail(RT_ERR_INVALID, "grid too large (element offsets must fit 32 bits)");
   if (layout < RT_GRID_AUTO || layout > RT_GRID_BRICKS) return fail(RT_ERR_INVALID, "unknown grid layout");
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
   if (rc) return rc;
+  DeviceGuard dg(s->reps[0]->device);
   s->kind = RT_SCENE_GRID;
-  s->dev.kind = RT_SCENE_GRID;
-  GridDev &g = s->dev.grid;
+  s->reps[0]->dev.kind = RT_SCENE_GRID;
+  GridDev &g = s->reps[0]->dev.grid;
   g.sx = sx; g.sy = sy; g.sz = sz;
   g.fx = (float)(sx - 1); g.fy = (float)(sy - 1); g.fz = (float)(sz - 1);
   g.hfx = 0.5f * g.fx; g.hfy = 0.5f * g.fy; g.hfz = 0.5f * g.fz;
@@ -212,7 +286,7 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
       scene_free(s);
       return fail(RT_ERR_CUDA, ierr);
     }
-    s->allocs.push_back(b);
+    adopt(s, b, count * sizeof(float));
     s->bytes += count * sizeof(float);
     g.values = b;
     g.bricks = 1; g.stride_x = nby * nbz * 512u; g.stride_y = nbz * 512u;
@@ -232,6 +306,7 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
   if (rc) return rc;
+  DeviceGuard dg(s->reps[0]->device);
   uint32_t *link = nullptr, depth = 0;
   float4 *vals = nullptr;
   std::string ierr;
@@ -240,32 +315,34 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
     scene_free(s);
     return fail(irc == INGEST_INVALID ? RT_ERR_INVALID : RT_ERR_CUDA, ierr);
   }
-  s->allocs.push_back(link);
-  s->allocs.push_back(vals);
+  adopt(s, link, (size_t)n_nodes * 4);
+  adopt(s, vals, (size_t)n_nodes * 32);
   s->bytes += (uint64_t)n_nodes * 36;
   s->kind = RT_SCENE_OCTREE;
-  s->dev.kind = RT_SCENE_OCTREE;
-  s->dev.oct.n_nodes = n_nodes;
-  s->dev.oct.depth = depth;
-  s->dev.oct.root_inner = depth > 0 ? 1u : 0u;
-  s->dev.oct.link = link;
-  s->dev.oct.values = vals;
+  OctreeDev &oc = s->reps[0]->dev.oct;
+  s->reps[0]->dev.kind = RT_SCENE_OCTREE;
+  oc.n_nodes = n_nodes;
+  oc.depth = depth;
+  oc.root_inner = depth > 0 ? 1u : 0u;
+  oc.link = link;
+  oc.values = vals;
   rc = scene_finish(s, out);
   if (rc != RT_OK) scene_free(s);
   return rc;
 }
 
 // ---------------------------------------------------------------------------------------------- mesh
-static int finish_mesh(HostBvh &h, bool brute, bool literal_order, rt_scene **out) {
+static int finish_mesh(HostBvh &h, bool literal_order, rt_scene **out) {
   rt_scene *s = nullptr;
   int rc = scene_begin(out, s);
   if (rc) return rc;
+  DeviceGuard dg(s->reps[0]->device);
   s->kind = RT_SCENE_MESH;
-  s->dev.kind = RT_SCENE_MESH;
-  MeshDev &m = s->dev.mesh;
+  s->reps[0]->dev.kind = RT_SCENE_MESH;
+  MeshDev &m = s->reps[0]->dev.mesh;
   m.n_tris = (uint32_t)h.tris.size();
   m.n_nodes = (uint32_t)h.nodes.size();
-  m.brute = brute ? 1u : 0u;
+  m.brute = h.brute;
   m.literal_order = literal_order ? 1u : 0u;
   for (int a = 0; a < 3; ++a) {
     s->bbox_min[a] = h.bbox_min[a];
@@ -286,6 +363,7 @@ int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *i
     rt_scene *s = nullptr;
     int rc = scene_begin(out, s);
     if (rc) return rc;
+    DeviceGuard dg(s->reps[0]->device);
     DeviceBvh d;
     std::string derr;
     if (!build_bvh8_device(vpos4, n_verts, indices, n_indices, d, derr)) {
@@ -295,12 +373,12 @@ int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *i
                       : RT_ERR_CUDA,
                   derr);
     }
-    s->allocs.push_back(d.nodes);
-    s->allocs.push_back(d.tris);
+    adopt(s, d.nodes, (size_t)d.n_nodes * sizeof(BvhNode));
+    adopt(s, d.tris, (size_t)d.n_tris * sizeof(TriDev));
     s->bytes += (uint64_t)d.n_nodes * sizeof(BvhNode) + (uint64_t)d.n_tris * sizeof(TriDev);
     s->kind = RT_SCENE_MESH;
-    s->dev.kind = RT_SCENE_MESH;
-    MeshDev &m = s->dev.mesh;
+    s->reps[0]->dev.kind = RT_SCENE_MESH;
+    MeshDev &m = s->reps[0]->dev.mesh;
     m.nodes = d.nodes;
     m.tris = d.tris;
     m.n_nodes = d.n_nodes;
@@ -317,13 +395,18 @@ int rt_scene_create_mesh(const float *vpos4, uint32_t n_verts, const uint32_t *i
     return rc;
   }
   if (accel == RT_MESH_LBVH_GPU) accel = RT_MESH_AUTO;  // tiny meshes: nothing to build
-  // brute force keeps the whole mesh in shared memory: 48 B per triangle, up to 4096 triangles (192 KB)
-  if (accel == RT_MESH_AUTO) accel = nTri <= 32 ? RT_MESH_BRUTE : RT_MESH_BVH8;
-  if (accel == RT_MESH_BRUTE && nTri > 4096) return fail(RT_ERR_UNSUPPORTED, "brute force is limited to 4096 triangles");
+  // Up to 8 triangles the reference's own tree is a single leaf whose triangles are tested without any box or range
+  // check (triangles_raytracing.cpp:175-186, 292-331): the brute-force kernel in BRUTE_ROOT_LEAF mode IS that, exactly,
+  // in every view.  Beyond 8 triangles only a tree reproduces the reference's box culling, so RT_MESH_AUTO builds one;
+  // RT_MESH_BRUTE stays available as an explicit choice (BRUTE_BOXED, rt_scene.h) up to 4096 triangles (192 KB of smem).
+  uint32_t brute = BRUTE_NONE;
+  if (nTri <= ROOT_LEAF_MAX_TRIS && accel != RT_MESH_BVH8) brute = BRUTE_ROOT_LEAF;
+  else if (accel == RT_MESH_BRUTE) brute = BRUTE_BOXED;
+  if (brute == BRUTE_BOXED && nTri > 4096) return fail(RT_ERR_UNSUPPORTED, "brute force is limited to 4096 triangles");
   HostBvh h;
   std::string err;
-  if (!build_bvh8(vpos4, n_verts, indices, n_indices, accel == RT_MESH_BRUTE, h, err)) return fail(RT_ERR_INVALID, err);
-  return finish_mesh(h, accel == RT_MESH_BRUTE, false, out);
+  if (!build_bvh8(vpos4, n_verts, indices, n_indices, brute, h, err)) return fail(RT_ERR_INVALID, err);
+  return finish_mesh(h, false, out);
 }
 
 int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32_t *indices_bvh, uint32_t n_indices,
@@ -334,7 +417,7 @@ int rt_scene_create_mesh_bvh8(const float *vpos4, uint32_t n_verts, const uint32
   if (!import_reference_bvh(vpos4, n_verts, indices_bvh, n_indices, nodes, n_nodes, node_bytes, prim_of_permuted, h,
                             err))
     return fail(RT_ERR_INVALID, err);
-  return finish_mesh(h, false, true, out);
+  return finish_mesh(h, true, out);
 }
 
 void rt_scene_destroy(rt_scene *scene) { scene_free(scene); }
@@ -347,14 +430,19 @@ int rt_scene_build_ms(const rt_scene *scene, float *device_ms) {
 
 int rt_scene_mesh_stats(const rt_scene *scene, uint32_t *n_nodes, uint32_t *n_tris, float *device_build_ms) {
   if (!scene || scene->kind != RT_SCENE_MESH) return fail(RT_ERR_INVALID, "not a mesh scene");
-  if (n_nodes) *n_nodes = scene->dev.mesh.n_nodes;
-  if (n_tris) *n_tris = scene->dev.mesh.n_tris;
+  if (n_nodes) *n_nodes = scene->reps[0]->dev.mesh.n_nodes;
+  if (n_tris) *n_tris = scene->reps[0]->dev.mesh.n_tris;
   if (device_build_ms) *device_build_ms = scene->build_ms;
   return RT_OK;
 }
 
 int rt_scene_kind_of(const rt_scene *scene) { return scene ? scene->kind : RT_ERR_INVALID; }
-int rt_scene_device(const rt_scene *scene) { return scene ? scene->device : RT_ERR_INVALID; }
+int rt_scene_device(const rt_scene *scene) { return scene ? scene->reps[0]->device : RT_ERR_INVALID; }
+int rt_scene_replicas(const rt_scene *scene, int *devices, int cap) {
+  if (!scene) return RT_ERR_INVALID;
+  for (size_t j = 0; j < scene->reps.size() && devices && (int)j < cap; ++j) devices[j] = scene->reps[j]->device;
+  return (int)scene->reps.size();
+}
 
 int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]) {
   if (!scene) return fail(RT_ERR_INVALID, "scene is null");
@@ -433,6 +521,8 @@ constexpr int HOST_ZEROCOPY_DEFAULT = 2;
 const int g_env_zero_copy = std::getenv("RT_HOST_ZEROCOPY") ? env_int("RT_HOST_ZEROCOPY") : HOST_ZEROCOPY_DEFAULT;
 const int g_env_oct_refill = env_int("RT_OCT_REFILL");
 const int g_env_oct_batch = env_int("RT_OCT_BATCH");
+// RT_MULTI=0: scenes with several replicas (rt_init) still render on one device per call (A/B measurements)
+const int g_env_multi = std::getenv("RT_MULTI") ? env_int("RT_MULTI") : 1;
 
 // per-scene-type default scheduling, chosen by measurement (profiles/r1_tune.txt): the octree
 // descent has the most uneven per-warp cost and gains from persistent warps pulling tiles; the grid marcher, the BVH
@@ -444,88 +534,336 @@ int resolve_sched(const rt_scene *s) {
   return RT_SCHED_TILES;
 }
 
-int render_on_stream(const rt_scene *scene, const FrameDev &fd, uint32_t *color, const float *t_in, float *t_out,
-                     uint32_t *prim, rt_counters *counters_dev, cudaStream_t st, int force_stage = -1) {
+// How the tiles of one launch reach the framebuffer.
+//   STORE_PLAIN : per-thread 32-byte tile-row stores (local HBM)
+//   STORE_AUTO  : STORE_PLAIN, except for a framebuffer opened with rt_ipc_open on a frame split over >= 8 ranks
+//   STORE_STAGED: the block's 32 x 4 pixels are parked in shared memory and leave as 128-byte TMA bulk stores
+//                 (peer HBM over NVLink, pinned host memory over PCIe); needs the fused clear, W % 8 == 0
+//   STORE_INOUT : STORE_STAGED for the reference's in/out framebuffer: the tile's previous contents are first fetched
+//                 with bulk loads, only nearer hits replace them
+enum StoreMode { STORE_AUTO = -1, STORE_PLAIN = 0, STORE_STAGED = 1, STORE_INOUT = 2 };
+
+// the staged kernels exist for every scene kind, with and without secondary rays and prim ids, under tiles scheduling;
+// the workload counters are only in the plain kernels
+bool staged_kernel_available(const FrameDev &fd, const void *counters) {
+  const int sched_now = g_sched.load();
+  return (sched_now == RT_SCHED_AUTO || sched_now == RT_SCHED_TILES) && !counters && fd.W % 8u == 0u;
+}
+
+int render_on_stream(const rt_scene *scene, Replica &rep, const FrameDev &fd, uint32_t *color, const float *t_in,
+                     float *t_out, uint32_t *prim, rt_counters *counters_dev, cudaStream_t st, int store = STORE_AUTO) {
   RenderArgs a;
-  a.scene = scene->dev;
+  a.scene = rep.dev;
   a.frame = fd;
   a.color = color;
   a.t_in = t_in;
   a.t_out = t_out;
   a.prim = prim;
   a.counters = reinterpret_cast<unsigned long long *>(counters_dev);
-  rt_scene *ms = const_cast<rt_scene *>(scene);
-  a.tile_counter = scene->tile_counters + (ms->next_counter.fetch_add(1) % N_TILE_COUNTERS);
+  a.tile_counter = rep.tile_counters + (rep.next_counter.fetch_add(1) % N_TILE_COUNTERS);
   a.tile_block = g_env_tile_block;
-  // Peer framebuffer (multi-GPU: rank 0's memory mapped over CUDA IPC): stage tiles in shared memory and store them as
-  // 128-byte TMA bulk writes.  Needs the fused clear (whole tiles are written) and 32-byte-multiple rows.
   a.stage_stores = 0;
   int sched = resolve_sched(scene);
-  // (force_stage, from rt_render_host with a pinned host framebuffer: 0 = plain stores, 1 = staged with the fused clear,
-  // 2 = staged in/out, the tile's previous contents fetched by bulk loads)
-  if ((fd.clear || force_stage == 2) && !prim && !counters_dev && fd.W % 8u == 0u &&
-      (force_stage >= 0 ? force_stage >= 1 : g_env_stage != 0)) {
-    bool peer = g_env_stage == 1 || force_stage >= 1;
-    // measured (profiles/r1_multi/TABLE.txt): pays when rank 0's inbound NVLink is saturated, i.e. on 8 GPUs at 4K
-    // (grid 0.139 -> 0.096 ms, bunny 0.147 -> 0.125 ms); not at 1080p (0.051 -> 0.053 ms), mixed on 4 GPUs (grid 0.131 ->
-    // 0.124, bunny 0.139 -> 0.165 ms) and slower on 2 (grid 0.196 -> 0.214 ms): the 32 x 4 block with its barrier is a
-    // slower kernel than the 16 x 8 one
-    if (!peer && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
-      peer = is_peer_pointer(color) && is_peer_pointer(t_out);
-    a.stage_stores = peer ? (force_stage == 2 ? 2 : 1) : 0;
-    if (peer && force_stage < 0) g_staged_launches.fetch_add(1);  // counts the multi-GPU path only
-    // the staged stores live in the tiles kernel: for a peer framebuffer the octree's default (persistent, ~1 % faster
-    // on one GPU) gives way to it
-    if (peer && g_sched.load() == RT_SCHED_AUTO) sched = RT_SCHED_TILES;
+  if ((fd.clear || store == STORE_INOUT) && staged_kernel_available(fd, counters_dev) &&
+      (store >= 0 ? store >= STORE_STAGED : g_env_stage != 0)) {
+    bool staged = g_env_stage == 1 || store >= STORE_STAGED;
+    // one process per GPU (rt_ipc_open): measured in round 1 (profiles/r1_multi/TABLE.txt) to pay when rank 0's inbound
+    // NVLink is saturated, i.e. on 8 GPUs at 4K
+    if (!staged && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
+      staged = is_peer_pointer(color) && is_peer_pointer(t_out);
+    a.stage_stores = staged ? (store == STORE_INOUT ? 2 : 1) : 0;
+    if (staged && store < 0) g_staged_launches.fetch_add(1);  // counts the one-process-per-GPU path only
+    // the staged stores live in the tiles kernel: the octree's default (persistent, ~1 % faster on one GPU) gives way
+    if (staged && g_sched.load() == RT_SCHED_AUTO) sched = RT_SCHED_TILES;
   }
   // RT_SCHED_COMPACT thresholds: best point of the sweep in profiles/r1_tune.txt (RT_OCT_REFILL / RT_OCT_BATCH override)
   a.oct_refill_min = g_env_oct_refill > 0 ? g_env_oct_refill : 32;
   a.oct_leaf_batch = g_env_oct_batch > 0 ? g_env_oct_batch : 6;
-  cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, scene->sm_count, st)
-                                                  : exact::launch_render(a, sched, scene->sm_count, st);
+  cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, rep.sm_count, st)
+                                                  : exact::launch_render(a, sched, rep.sm_count, st);
   if (e != cudaSuccess) return cuda_fail(e, "render launch");
   return RT_OK;
 }
 
-// Device-side address of a pinned (page-locked, mapped) host buffer, or null for pageable / device memory.
-void *mapped_host_pointer(const void *p) {
-  cudaPointerAttributes at;
+// Device-side address of a pinned (page-locked, mapped) host range [p, p + bytes), or null for pageable / device
+// memory, a range that is only partly registered, or one the bulk copies cannot address (16-byte alignment).
+void *mapped_host_range(const void *p, size_t bytes) {
+  cudaPointerAttributes at, last;
   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
     cudaGetLastError();
     return nullptr;
   }
-  return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+  if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+  const char *end = static_cast<const char *>(p) + (bytes ? bytes - 1 : 0);
+  if (cudaPointerGetAttributes(&last, end) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  if (last.type != cudaMemoryTypeHost ||
+      static_cast<char *>(last.devicePointer) != static_cast<char *>(at.devicePointer) + (bytes ? bytes - 1 : 0))
+    return nullptr;
+  if (reinterpret_cast<uintptr_t>(at.devicePointer) % 16u) return nullptr;
+  return at.devicePointer;
 }
 
-int ensure_host_buffers(rt_scene *s, size_t pixels) {
-  if (!s->h_cnt) {  // created last: a call that failed half-way is completed by the next one
-    if (!s->h_stream) RT_CUDA(cudaStreamCreateWithFlags(&s->h_stream, cudaStreamNonBlocking));
-    if (!s->h_up) RT_CUDA(cudaStreamCreateWithFlags(&s->h_up, cudaStreamNonBlocking));
-    if (!s->h_down) RT_CUDA(cudaStreamCreateWithFlags(&s->h_down, cudaStreamNonBlocking));
-    for (auto &e : s->ev)
-      if (!e) RT_CUDA(cudaEventCreate(&e));
-    for (auto &e : s->ev_up)
-      if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    for (auto &e : s->ev_k)
-      if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    RT_CUDA(cudaMalloc(&s->h_cnt, sizeof(rt_counters)));
+// streams and events of a replica (current device = rep.device)
+int ensure_streams(Replica &r) {
+  if (r.h_cnt) return RT_OK;  // created last: a call that failed half-way is completed by the next one
+  if (!r.h_stream) RT_CUDA(cudaStreamCreateWithFlags(&r.h_stream, cudaStreamNonBlocking));
+  if (!r.h_up) RT_CUDA(cudaStreamCreateWithFlags(&r.h_up, cudaStreamNonBlocking));
+  if (!r.h_down) RT_CUDA(cudaStreamCreateWithFlags(&r.h_down, cudaStreamNonBlocking));
+  for (auto &e : r.ev)
+    if (!e) RT_CUDA(cudaEventCreate(&e));
+  for (auto &e : r.ev_up)
+    if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (auto &e : r.ev_k)
+    if (!e) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  if (!r.ev_fork) RT_CUDA(cudaEventCreateWithFlags(&r.ev_fork, cudaEventDisableTiming));
+  if (!r.ev_join) RT_CUDA(cudaEventCreateWithFlags(&r.ev_join, cudaEventDisableTiming));
+  RT_CUDA(cudaMalloc(&r.h_cnt, sizeof(rt_counters)));
+  return RT_OK;
+}
+
+// device framebuffer of the copy pipeline: only the paths that copy allocate it (12 bytes per pixel)
+int ensure_device_fb(Replica &r, size_t pixels) {
+  if (pixels <= r.h_pixels) return RT_OK;
+  if (r.h_color) cudaFree(r.h_color);
+  if (r.h_t) cudaFree(r.h_t);
+  if (r.h_prim) cudaFree(r.h_prim);
+  r.h_color = nullptr; r.h_t = nullptr; r.h_prim = nullptr; r.h_pixels = 0;
+  RT_CUDA(cudaMalloc(&r.h_color, pixels * 4));
+  RT_CUDA(cudaMalloc(&r.h_t, pixels * 4));
+  RT_CUDA(cudaMalloc(&r.h_prim, pixels * 4));
+  r.h_pixels = pixels;
+  return RT_OK;
+}
+
+Replica *replica_on(const rt_scene *s, int device) {
+  for (auto &r : s->reps)
+    if (r->device == device) return r.get();
+  return nullptr;
+}
+
+// rows per interleaved band when ONE call fans a frame out over the replicas (a multiple of the 4-row staged block;
+// hit density is mid-screen, so contiguous slabs would load-imbalance: SURVEY 8(e))
+uint32_t multi_band_rows() {
+  static const int v = env_int("RT_MULTI_BAND_ROWS");
+  return v > 0 ? (uint32_t)((v + 3) & ~3) : 8u;
+}
+
+// frame parameters of replica j's share of a whole frame split over n devices
+FrameDev band_share(const FrameDev &whole, uint32_t n, uint32_t j) {
+  FrameDev f = whole;
+  f.band_rows = multi_band_rows();
+  f.band_count = n;
+  f.band_index = j;
+  const uint32_t nBands = (f.H + f.band_rows - 1) / f.band_rows;
+  const uint32_t mine = nBands > j ? (nBands - j + n - 1) / n : 0;
+  f.rows_here = mine * f.band_rows;
+  return f;
+}
+
+// Copies the interleaved bands of replica j between a host frame and the device frame of the same layout, as ONE
+// strided 2-D copy per buffer (band k of share j starts at row (k * n + j) * band_rows) plus the frame's ragged tail.
+int copy_bands(void *dst, const void *src, const FrameDev &f, cudaMemcpyKind kind, cudaStream_t st) {
+  const size_t rowBytes = (size_t)f.W * 4, bandBytes = rowBytes * f.band_rows, pitch = bandBytes * f.band_count;
+  const uint32_t nBands = (f.H + f.band_rows - 1) / f.band_rows;
+  uint32_t mine = nBands > f.band_index ? (nBands - f.band_index + f.band_count - 1) / f.band_count : 0;
+  if (mine == 0) return RT_OK;
+  const size_t off = bandBytes * f.band_index;
+  const uint32_t lastRow0 = ((mine - 1) * f.band_count + f.band_index) * f.band_rows;  // first row of my last band
+  const uint32_t lastRows = std::min(f.band_rows, f.H - lastRow0);
+  const uint32_t full = lastRows == f.band_rows ? mine : mine - 1;
+  if (full)
+    RT_CUDA(cudaMemcpy2DAsync(static_cast<char *>(dst) + off, pitch, static_cast<const char *>(src) + off, pitch,
+                              bandBytes, full, kind, st));
+  if (full != mine)
+    RT_CUDA(cudaMemcpyAsync(static_cast<char *>(dst) + (size_t)lastRow0 * rowBytes,
+                            static_cast<const char *>(src) + (size_t)lastRow0 * rowBytes, (size_t)lastRows * rowBytes, kind,
+                            st));
+  return RT_OK;
+}
+
+double wall_ms_since(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// ---- Renderer::draw from ONE call over every replica: host framebuffer ----------------------------------------------
+// Each device renders its interleaved bands.  Pinned framebuffer: each kernel stores (and, for the in/out contract,
+// first loads) its tiles straight in the caller's buffers over ITS OWN PCIe link, so n devices bring n links to a
+// transfer that bounds the single-device call (0.35 ms of 1080p frame against a 0.11 ms kernel).  Anything else:
+// per-device framebuffers, one strided copy per buffer and direction.
+int render_host_multi(rt_scene *s, const FrameDev &fd, uint32_t *color, float *t_inout, uint32_t *prim,
+                      float *device_ms, float *total_ms, rt_counters *counters) {
+  const auto t0 = std::chrono::steady_clock::now();
+  const uint32_t n = (uint32_t)s->reps.size();
+  const size_t pixels = (size_t)fd.W * fd.H, bytes = pixels * 4;
+  const bool inout = !fd.clear;
+  struct Drain {
+    rt_scene *s;
+    bool armed = true;
+    ~Drain() {
+      if (!armed) return;
+      for (auto &r : s->reps) {
+        DeviceGuard g(r->device);
+        if (r->h_stream) cudaStreamSynchronize(r->h_stream);
+      }
+    }
+  } drain{s};
+  for (auto &r : s->reps) {
+    DeviceGuard g(r->device);
+    if (!g.ok) return fail(RT_ERR_CUDA, "cannot select a replica's device");
+    int rc = ensure_streams(*r);
+    if (rc) return rc;
   }
-  if (pixels > s->h_pixels) {
-    if (s->h_color) cudaFree(s->h_color);
-    if (s->h_t) cudaFree(s->h_t);
-    if (s->h_prim) cudaFree(s->h_prim);
-    s->h_color = nullptr; s->h_t = nullptr; s->h_prim = nullptr; s->h_pixels = 0;
-    RT_CUDA(cudaMalloc(&s->h_color, pixels * 4));
-    RT_CUDA(cudaMalloc(&s->h_t, pixels * 4));
-    RT_CUDA(cudaMalloc(&s->h_prim, pixels * 4));
-    s->h_pixels = pixels;
+  const bool timing = device_ms != nullptr;
+  uint32_t *dc = nullptr;
+  float *dt = nullptr;
+  uint32_t *dp = nullptr;
+  if (g_env_zero_copy != 0 && staged_kernel_available(fd, counters) && (inout ? g_env_zero_copy == 2 : true)) {
+    dc = static_cast<uint32_t *>(mapped_host_range(color, bytes));
+    dt = static_cast<float *>(mapped_host_range(t_inout, bytes));
+    if (prim) dp = static_cast<uint32_t *>(mapped_host_range(prim, bytes));
   }
+  const bool direct = dc && dt && (!prim || dp);
+  for (uint32_t j = 0; j < n; ++j) {
+    Replica &r = *s->reps[j];
+    DeviceGuard g(r.device);
+    const FrameDev fj = band_share(fd, n, j);
+    cudaStream_t st = r.h_stream;
+    int rc = RT_OK;
+    if (direct) {
+      if (timing) RT_CUDA(cudaEventRecord(r.ev[0], st));
+      rc = render_on_stream(s, r, fj, dc, inout ? dt : nullptr, dt, dp, nullptr, st,
+                            inout ? STORE_INOUT : (g_env_zero_copy >= 2 ? STORE_STAGED : STORE_PLAIN));
+      if (rc) return rc;
+      if (timing) RT_CUDA(cudaEventRecord(r.ev[3], st));
+      continue;
+    }
+    rc = ensure_device_fb(r, pixels);
+    if (rc) return rc;
+    if (inout) {
+      if ((rc = copy_bands(r.h_t, t_inout, fj, cudaMemcpyHostToDevice, st))) return rc;
+      if ((rc = copy_bands(r.h_color, color, fj, cudaMemcpyHostToDevice, st))) return rc;
+    }
+    if (prim && inout) RT_CUDA(cudaMemsetAsync(r.h_prim, 0xFF, bytes, st));  // pixels not written: MISS
+    if (counters) RT_CUDA(cudaMemsetAsync(r.h_cnt, 0, sizeof(rt_counters), st));
+    if (timing) RT_CUDA(cudaEventRecord(r.ev[0], st));
+    rc = render_on_stream(s, r, fj, r.h_color, r.h_t, r.h_t, prim ? r.h_prim : nullptr, counters ? r.h_cnt : nullptr, st,
+                          STORE_PLAIN);
+    if (rc) return rc;
+    if (timing) RT_CUDA(cudaEventRecord(r.ev[3], st));
+    if ((rc = copy_bands(color, r.h_color, fj, cudaMemcpyDeviceToHost, st))) return rc;
+    if ((rc = copy_bands(t_inout, r.h_t, fj, cudaMemcpyDeviceToHost, st))) return rc;
+    if (prim && (rc = copy_bands(prim, r.h_prim, fj, cudaMemcpyDeviceToHost, st))) return rc;
+  }
+  if (counters) std::memset(counters, 0, sizeof *counters);
+  float worst = 0.0f;
+  for (uint32_t j = 0; j < n; ++j) {
+    Replica &r = *s->reps[j];
+    DeviceGuard g(r.device);
+    RT_CUDA(cudaStreamSynchronize(r.h_stream));
+    if (timing) {
+      float ms = 0.0f;
+      RT_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[3]));
+      worst = std::max(worst, ms);
+    }
+    if (counters) {
+      rt_counters c;
+      RT_CUDA(cudaMemcpy(&c, r.h_cnt, sizeof c, cudaMemcpyDeviceToHost));
+      const uint64_t *src = reinterpret_cast<const uint64_t *>(&c);
+      uint64_t *dst = reinterpret_cast<uint64_t *>(counters);
+      for (size_t k = 0; k < sizeof(rt_counters) / sizeof(uint64_t); ++k) dst[k] += src[k];
+    }
+  }
+  drain.armed = false;
+  if (device_ms) *device_ms = worst;  // the slowest device's kernel: the frame is done when the last band is
+  if (total_ms) *total_ms = (float)wall_ms_since(t0);
+  return RT_OK;
+}
+
+// ---- the same on a DEVICE-resident framebuffer: tiles gathered over NVLink inside the render kernels ----------------
+// The framebuffer lives on one of the replicas' devices (the owner).  The owner renders its bands on the caller's
+// stream; every other replica waits for the caller's stream (event fork), renders its bands with the tile staged in
+// shared memory and stored into the owner's HBM as 128-byte bulk writes over NVLink (peer access enabled by rt_init),
+// and the caller's stream waits for all of them (event join).  Asynchronous like the single-device call.
+int render_device_multi(const rt_scene *s, Replica &owner, const FrameDev &fd, uint32_t *color, const float *t_in,
+                        float *t_out, uint32_t *prim, cudaStream_t user) {
+  const uint32_t n = (uint32_t)s->reps.size();
+  for (auto &r : s->reps) {
+    DeviceGuard g(r->device);
+    if (!g.ok) return fail(RT_ERR_CUDA, "cannot select a replica's device");
+    int rc = ensure_streams(*r);
+    if (rc) return rc;
+  }
+  const bool inout = !fd.clear && t_in != nullptr;
+  const bool can_stage = staged_kernel_available(fd, nullptr) && (fd.clear || inout) && g_env_stage != 0 &&
+                         reinterpret_cast<uintptr_t>(color) % 16u == 0 && reinterpret_cast<uintptr_t>(t_out) % 16u == 0 &&
+                         reinterpret_cast<uintptr_t>(prim) % 16u == 0 && (!inout || t_in == t_out);
+  {
+    DeviceGuard g(owner.device);
+    RT_CUDA(cudaEventRecord(owner.ev_fork, user));
+  }
+  for (uint32_t j = 0; j < n; ++j) {
+    Replica &r = *s->reps[j];
+    const FrameDev fj = band_share(fd, n, j);
+    DeviceGuard g(r.device);
+    if (&r == &owner) {
+      int rc = render_on_stream(s, r, fj, color, t_in, t_out, prim, nullptr, user, STORE_PLAIN);
+      if (rc) return rc;
+      continue;
+    }
+    RT_CUDA(cudaStreamWaitEvent(r.h_stream, owner.ev_fork, 0));
+    int rc = render_on_stream(s, r, fj, color, t_in, t_out, prim, nullptr, r.h_stream,
+                              can_stage ? (inout ? STORE_INOUT : STORE_STAGED) : STORE_PLAIN);
+    if (rc) return rc;
+    RT_CUDA(cudaEventRecord(r.ev_join, r.h_stream));
+  }
+  DeviceGuard g(owner.device);
+  for (auto &r : s->reps)
+    if (r.get() != &owner) RT_CUDA(cudaStreamWaitEvent(user, r->ev_join, 0));
   return RT_OK;
 }
 
 }  // namespace
 
 extern "C" {
+
+// ---- multi-GPU from one process (rt_init(devs, n)) ------------------------------------------------------
+int rt_init(const int *devices, int n) {
+  if (n < 0 || (n > 0 && !devices)) return fail(RT_ERR_INVALID, "bad device list");
+  int count = 0;
+  RT_CUDA(cudaGetDeviceCount(&count));
+  std::vector<int> devs(devices, devices + n);
+  for (int i = 0; i < n; ++i) {
+    if (devs[i] < 0 || devs[i] >= count) return fail(RT_ERR_INVALID, "device index out of range");
+    for (int k = 0; k < i; ++k)
+      if (devs[k] == devs[i]) return fail(RT_ERR_INVALID, "device listed twice");
+  }
+  // peer access both ways between every pair: the device-resident fan-out stores tiles into the owner's HBM
+  for (int i = 0; i < n; ++i) {
+    DeviceGuard g(devs[i]);
+    if (!g.ok) return fail(RT_ERR_CUDA, "cannot select a listed device");
+    for (int k = 0; k < n; ++k) {
+      if (k == i) continue;
+      int can = 0;
+      RT_CUDA(cudaDeviceCanAccessPeer(&can, devs[i], devs[k]));
+      if (!can) continue;  // no NVLink / PCIe peer path: rt_render_device then keeps such a pair apart (plain copies)
+      cudaError_t e = cudaDeviceEnablePeerAccess(devs[k], 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+    }
+  }
+  std::lock_guard<std::mutex> lock(g_dev_mu);
+  g_devs = devs;
+  return RT_OK;
+}
+
+int rt_device_list(int *devices, int cap) {
+  std::lock_guard<std::mutex> lock(g_dev_mu);
+  for (size_t j = 0; j < g_devs.size() && devices && (int)j < cap; ++j) devices[j] = g_devs[j];
+  return (int)g_devs.size();
+}
 
 int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *color, const float *t_in, float *t_out,
                      uint32_t *prim, rt_counters *counters_dev, void *stream) {
@@ -534,9 +872,32 @@ int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *col
   FrameDev fd;
   int rc = make_frame(frame, fd);
   if (rc) return rc;
-  DeviceGuard g(scene->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (scene->reps.size() > 1) {
+    // where does the framebuffer live?  (a pointer opened with rt_ipc_open reports the mapping device: the one-process-
+    // per-GPU path, which partitions the frame itself)
+    cudaPointerAttributes at;
+    Replica *owner = nullptr;
+    if (cudaPointerGetAttributes(&at, color) == cudaSuccess && at.type == cudaMemoryTypeDevice)
+      owner = replica_on(scene, at.device);
+    else
+      cudaGetLastError();
+    if (owner && fd.band_count <= 1 && !counters_dev && !is_peer_pointer(color) && g_env_multi != 0)
+      return render_device_multi(scene, *owner, fd, color, t_in, t_out, prim, st);
+    if (!owner) {
+      int cur = 0;
+      RT_CUDA(cudaGetDevice(&cur));
+      owner = replica_on(scene, cur);
+    }
+    if (!owner) owner = scene->reps[0].get();
+    DeviceGuard g(owner->device);
+    if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
+    return render_on_stream(scene, *owner, fd, color, t_in, t_out, prim, counters_dev, st);
+  }
+  Replica &r = *scene->reps[0];
+  DeviceGuard g(r.device);
   if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
-  return render_on_stream(scene, fd, color, t_in, t_out, prim, counters_dev, static_cast<cudaStream_t>(stream));
+  return render_on_stream(scene, r, fd, color, t_in, t_out, prim, counters_dev, st);
 }
 
 int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,
@@ -547,54 +908,56 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
   int rc = make_frame(frame, fd);
   if (rc) return rc;
   rt_scene *s = const_cast<rt_scene *>(scene_c);
-  DeviceGuard g(s->device);
-  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
   std::lock_guard<std::mutex> lock(s->host_mu);
+  // one call, every device of rt_init's list (a caller that partitions the frame itself keeps the single-device path)
+  if (s->reps.size() > 1 && fd.band_count <= 1 && g_env_multi != 0)
+    return render_host_multi(s, fd, color, t_inout, prim, device_ms, total_ms, counters);
+  Replica &r = *s->reps[0];
+  DeviceGuard g(r.device);
+  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
   const size_t pixels = (size_t)fd.W * fd.H, bytes = pixels * 4;
-  rc = ensure_host_buffers(s, pixels);
+  rc = ensure_streams(r);
   if (rc) return rc;
-  cudaStream_t st = s->h_stream;
+  cudaStream_t st = r.h_stream;
   // An error return must not leave copies into the caller's buffers in flight: drain the three streams on the way out.
   struct Drain {
-    rt_scene *s;
+    Replica *r;
     bool armed = true;
     ~Drain() {
       if (!armed) return;
-      cudaStreamSynchronize(s->h_up);
-      cudaStreamSynchronize(s->h_stream);
-      cudaStreamSynchronize(s->h_down);
+      cudaStreamSynchronize(r->h_up);
+      cudaStreamSynchronize(r->h_stream);
+      cudaStreamSynchronize(r->h_down);
     }
-  } drain{s};
-  // Pinned host framebuffer, whole frame overwritten, nothing else asked for: the kernel stores its tiles straight into
-  // the caller's buffers over PCIe (no device framebuffer, no copy engine, one launch).
-  // (mode 2 needs the launch to be the staged tiles kernel: primary rays, not the brute-force mesh, tiles scheduling;
-  // everything else keeps the copies, which beat plain 32-byte stores over PCIe)
-  const bool secondary = fd.mode == RT_SHADE_LAMBERT && (fd.shadows || fd.reflections);
-  const int sched_now = g_sched.load();
-  const bool staged_ok = !secondary && !(s->kind == RT_SCENE_MESH && s->dev.mesh.brute) &&
-                         (sched_now == RT_SCHED_AUTO || sched_now == RT_SCHED_TILES);
-  // The in/out contract (clear = 0) takes the same route in mode 2: the kernel fetches each tile's previous colour and
-  // depth from the host buffers with bulk loads and sends the merged tile back.
+  } drain{&r};
+  // Pinned host framebuffer (colour, depth and, when asked for, prim ids): the kernel works on the caller's buffers over PCIe
+  // (no device framebuffer, no copy engine, one launch).  clear = 1: tiles leave as 128-byte bulk stores; clear = 0 (the
+  // reference's in/out contract): the tile's previous colour and depth are fetched with bulk loads first.  Banded calls
+  // take the same route (the staged kernel walks the call's bands).  Mode 1 = plain 32-byte stores (measurements only).
   const bool inout = !fd.clear;
+  const bool staged_ok = staged_kernel_available(fd, counters);
   if (g_env_zero_copy != 0 && (inout ? (g_env_zero_copy == 2 && staged_ok) : (g_env_zero_copy == 1 || staged_ok)) &&
-      fd.band_count <= 1 && !prim && !counters && fd.W % 8u == 0u) {
-    uint32_t *dc = static_cast<uint32_t *>(mapped_host_pointer(color));
-    float *dt = static_cast<float *>(mapped_host_pointer(t_inout));
-    if (dc && dt) {
-      RT_CUDA(cudaEventRecord(s->ev[0], st));
-      rc = render_on_stream(s, fd, dc, inout ? dt : nullptr, dt, nullptr, nullptr, st,
-                            inout ? 2 : (g_env_zero_copy >= 2 ? 1 : 0));
+      !counters && fd.W % 8u == 0u && (fd.band_count <= 1 || fd.band_rows % 4u == 0u)) {
+    uint32_t *dc = static_cast<uint32_t *>(mapped_host_range(color, bytes));
+    float *dt = static_cast<float *>(mapped_host_range(t_inout, bytes));
+    uint32_t *dp = prim ? static_cast<uint32_t *>(mapped_host_range(prim, bytes)) : nullptr;
+    if (dc && dt && (!prim || dp)) {
+      RT_CUDA(cudaEventRecord(r.ev[0], st));
+      rc = render_on_stream(s, r, fd, dc, inout ? dt : nullptr, dt, dp, nullptr, st,
+                            inout ? STORE_INOUT : (g_env_zero_copy >= 2 && staged_ok ? STORE_STAGED : STORE_PLAIN));
       if (rc) return rc;
-      RT_CUDA(cudaEventRecord(s->ev[3], st));
+      RT_CUDA(cudaEventRecord(r.ev[3], st));
       RT_CUDA(cudaStreamSynchronize(st));
       float ms = 0.0f;
-      if (device_ms || total_ms) RT_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[3]));
+      if (device_ms || total_ms) RT_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[3]));
       if (device_ms) *device_ms = ms;
       if (total_ms) *total_ms = ms;
       drain.armed = false;
       return RT_OK;
     }
   }
+  rc = ensure_device_fb(r, pixels);
+  if (rc) return rc;
   // The frame is cut into row chunks that flow through three streams: upload (only when the caller's depth /
   // colour matter: the framebuffer is in/out, raytracing.cpp:17,90-94), render, download.  The PCIe copies of one
   // chunk overlap the kernel of the next, so the call costs ~max(copy time, kernel time), not their sum.
@@ -613,22 +976,22 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
       const uint32_t rows = (fd.H + n_chunks - 1) / n_chunks;
       for (uint32_t k = 1; k <= n_chunks; ++k) bounds[k] = std::min(fd.H, k * rows);
     } else {
-      uint32_t rows = std::max<uint32_t>(16u, fd.H / 40u), r = 0;
+      uint32_t rows = std::max<uint32_t>(16u, fd.H / 40u), r0 = 0;
       n_chunks = 0;
-      while (r < fd.H && n_chunks < 15) {
-        r = std::min(fd.H, r + rows);
-        if (fd.H - r < rows) r = fd.H;  // fold a short remainder into this chunk
-        bounds[++n_chunks] = r;
+      while (r0 < fd.H && n_chunks < 15) {
+        r0 = std::min(fd.H, r0 + rows);
+        if (fd.H - r0 < rows) r0 = fd.H;  // fold a short remainder into this chunk
+        bounds[++n_chunks] = r0;
         rows *= 2;
       }
-      if (r < fd.H) bounds[++n_chunks] = fd.H;
+      if (r0 < fd.H) bounds[++n_chunks] = fd.H;
     }
   }
-  RT_CUDA(cudaEventRecord(s->ev[0], st));
-  if (prim && need_upload) RT_CUDA(cudaMemsetAsync(s->h_prim, 0xFF, bytes, st));  // rows not rendered: MISS
-  if (counters) RT_CUDA(cudaMemsetAsync(s->h_cnt, 0, sizeof(rt_counters), st));
-  RT_CUDA(cudaEventRecord(s->ev[1], st));
-  RT_CUDA(cudaStreamWaitEvent(s->h_up, s->ev[0], 0));
+  RT_CUDA(cudaEventRecord(r.ev[0], st));
+  if (prim && need_upload) RT_CUDA(cudaMemsetAsync(r.h_prim, 0xFF, bytes, st));  // rows not rendered: MISS
+  if (counters) RT_CUDA(cudaMemsetAsync(r.h_cnt, 0, sizeof(rt_counters), st));
+  RT_CUDA(cudaEventRecord(r.ev[1], st));
+  RT_CUDA(cudaStreamWaitEvent(r.h_up, r.ev[0], 0));
   for (uint32_t k = 0; k < n_chunks; ++k) {
     const uint32_t r0 = bounds[k], r1 = bounds[k + 1];
     if (r0 >= r1) continue;
@@ -640,27 +1003,28 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
     }
     if (need_upload) {
       const size_t uoff = n_chunks > 1 ? off : 0, ubytes = n_chunks > 1 ? cbytes : bytes;
-      RT_CUDA(cudaMemcpyAsync(s->h_t + uoff, t_inout + uoff, ubytes, cudaMemcpyHostToDevice, s->h_up));
-      RT_CUDA(cudaMemcpyAsync(s->h_color + uoff, color + uoff, ubytes, cudaMemcpyHostToDevice, s->h_up));
-      RT_CUDA(cudaEventRecord(s->ev_up[k], s->h_up));
-      RT_CUDA(cudaStreamWaitEvent(st, s->ev_up[k], 0));
+      RT_CUDA(cudaMemcpyAsync(r.h_t + uoff, t_inout + uoff, ubytes, cudaMemcpyHostToDevice, r.h_up));
+      RT_CUDA(cudaMemcpyAsync(r.h_color + uoff, color + uoff, ubytes, cudaMemcpyHostToDevice, r.h_up));
+      RT_CUDA(cudaEventRecord(r.ev_up[k], r.h_up));
+      RT_CUDA(cudaStreamWaitEvent(st, r.ev_up[k], 0));
     }
-    rc = render_on_stream(s, fk, s->h_color, s->h_t, s->h_t, prim ? s->h_prim : nullptr, counters ? s->h_cnt : nullptr, st);
+    rc = render_on_stream(s, r, fk, r.h_color, r.h_t, r.h_t, prim ? r.h_prim : nullptr, counters ? r.h_cnt : nullptr, st,
+                          STORE_PLAIN);
     if (rc) return rc;
-    RT_CUDA(cudaEventRecord(s->ev_k[k], st));
-    RT_CUDA(cudaStreamWaitEvent(s->h_down, s->ev_k[k], 0));
+    RT_CUDA(cudaEventRecord(r.ev_k[k], st));
+    RT_CUDA(cudaStreamWaitEvent(r.h_down, r.ev_k[k], 0));
     const size_t doff = n_chunks > 1 ? off : 0, dbytes = n_chunks > 1 ? cbytes : bytes;
-    RT_CUDA(cudaMemcpyAsync(color + doff, s->h_color + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
-    RT_CUDA(cudaMemcpyAsync(t_inout + doff, s->h_t + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
-    if (prim) RT_CUDA(cudaMemcpyAsync(prim + doff, s->h_prim + doff, dbytes, cudaMemcpyDeviceToHost, s->h_down));
+    RT_CUDA(cudaMemcpyAsync(color + doff, r.h_color + doff, dbytes, cudaMemcpyDeviceToHost, r.h_down));
+    RT_CUDA(cudaMemcpyAsync(t_inout + doff, r.h_t + doff, dbytes, cudaMemcpyDeviceToHost, r.h_down));
+    if (prim) RT_CUDA(cudaMemcpyAsync(prim + doff, r.h_prim + doff, dbytes, cudaMemcpyDeviceToHost, r.h_down));
   }
-  RT_CUDA(cudaEventRecord(s->ev[2], st));
-  if (counters) RT_CUDA(cudaMemcpyAsync(counters, s->h_cnt, sizeof(rt_counters), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaEventRecord(r.ev[2], st));
+  if (counters) RT_CUDA(cudaMemcpyAsync(counters, r.h_cnt, sizeof(rt_counters), cudaMemcpyDeviceToHost, st));
   RT_CUDA(cudaStreamSynchronize(st));
-  RT_CUDA(cudaEventRecord(s->ev[3], s->h_down));
-  RT_CUDA(cudaStreamSynchronize(s->h_down));
-  if (device_ms) RT_CUDA(cudaEventElapsedTime(device_ms, s->ev[1], s->ev[2]));
-  if (total_ms) RT_CUDA(cudaEventElapsedTime(total_ms, s->ev[0], s->ev[3]));
+  RT_CUDA(cudaEventRecord(r.ev[3], r.h_down));
+  RT_CUDA(cudaStreamSynchronize(r.h_down));
+  if (device_ms) RT_CUDA(cudaEventElapsedTime(device_ms, r.ev[1], r.ev[2]));
+  if (total_ms) RT_CUDA(cudaEventElapsedTime(total_ms, r.ev[0], r.ev[3]));
   drain.armed = false;  // both syncs above succeeded: nothing is pending
   return RT_OK;
 }
@@ -671,7 +1035,8 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
   if (!scene) return fail(RT_ERR_INVALID, "scene is null");
   if (n == 0) return RT_OK;
   if (!origins || !dirs) return fail(RT_ERR_INVALID, "origins / dirs must not be null");
-  DeviceGuard g(scene->device);
+  const Replica &r0 = *scene->reps[0];
+  DeviceGuard g(r0.device);
   if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
   float *dO = nullptr, *dD = nullptr, *dT = nullptr, *dN = nullptr;
   uint8_t *dH = nullptr;
@@ -694,7 +1059,7 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
   RT_TRY(cudaMemcpy(dO, origins, (size_t)n * 12, cudaMemcpyHostToDevice));
   RT_TRY(cudaMemcpy(dD, dirs, (size_t)n * 12, cudaMemcpyHostToDevice));
   RayArgs a;
-  a.scene = scene->dev;
+  a.scene = r0.dev;
   a.origins = dO; a.dirs = dD; a.n = n;
   a.t_near = t_near; a.t_far = t_far;
   a.has_plane = has_plane != 0; a.plane_y = plane_y;

@@ -800,11 +800,14 @@ __device__ __forceinline__ Hit brute_intersect(const MeshDev &m, const float4 *s
                                                float tFar, Counters &cnt) {
   Hit r = hit_none();
   const uint32_t nTris = m.n_tris;
-  // The reference only reaches triangles through boxes that pass intersect_box_8 against [tNear, tFar] (a box wholly
-  // behind the origin or beyond tFar is culled, triangles_raytracing.cpp:266-297); all of them lie inside the mesh's
-  // bounding box, which is lane 0 of the single node a brute-force scene carries: a ray that fails this test hits
-  // nothing there (looking away from the mesh, or the framebuffer already holding a nearer depth).
-  {
+  // BRUTE_ROOT_LEAF (<= 8 triangles): the reference's tree is one leaf, and traverseNode(0) on a leaf tests its
+  // triangles with no box test and no range check at all (triangles_raytracing.cpp:292-331): nothing to cull here.
+  // BRUTE_BOXED (explicit RT_MESH_BRUTE on 9+ triangles): the reference only reaches triangles through child boxes that
+  // pass intersect_box_8 against [tNear, tFar] (:271-291); all of them lie inside the mesh's bounding box, lane 0 of
+  // the single node such a scene carries, so a ray that fails the same test on it hits nothing there, and `th <= tFar`
+  // stands in for the leaf boxes' own cull.  Tree-independent views only (rt_scene.h).
+  const bool boxed = m.brute == BRUTE_BOXED;
+  if (boxed) {
     const BvhNode *n = m.nodes;
     const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     if (slab_lane<false>(__ldg(&n->lo[0][0]), __ldg(&n->lo[1][0]), __ldg(&n->lo[2][0]), __ldg(&n->hi[0][0]),
@@ -816,11 +819,7 @@ __device__ __forceinline__ Hit brute_intersect(const MeshDev &m, const float4 *s
     if (COUNT) cnt.bvh_tris++;
     const float4 a = smemTris[3 * k], bq = smemTris[3 * k + 1], cq = smemTris[3 * k + 2];
     float th;
-    // th <= tFar stands in for the reference's box culling: its leaf boxes hug the faces of a small mesh, so a hit
-    // beyond tFar (= the depth already in the framebuffer) never survives there, while hits in front of tNear and
-    // behind the origin do (triangle hits themselves are not range-checked).  Checked against the compiled
-    // reference on the cube from outside and inside, cleared and pre-filled depth (tests/test_host_emul.py).
-    if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && th <= tFar && (!r.hitten || r.t > th)) {
+    if (tri_lane(o, d, ld3(a), ld3(bq), ld3(cq), th) && (!boxed || th <= tFar) && (!r.hitten || r.t > th)) {
       r.hitten = true;
       r.t = th;
       best = k;

@@ -125,26 +125,32 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
 }
 
 // ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (peer or pinned-host framebuffer) --------
-// When the framebuffer lives on ANOTHER GPU (rank 0's, mapped over CUDA IPC) or in page-locked HOST memory
-// (rt_render_host), the plain kernel's stores cross NVLink / PCIe as 32-byte pieces (one 8-pixel tile row per warp).
-// Here a block owns 32 x 4 pixels: every thread parks its pixel in shared memory, and after one barrier four threads
-// issue the block's eight 128-byte row segments (colour + depth) as bulk asynchronous stores (cp.async.bulk shared ->
-// global, SASS UBLKCP): full 128-byte writes, no per-thread store instructions.  W % 8 == 0; primary rays only.
+// When the framebuffer lives on ANOTHER GPU (peer access / CUDA IPC) or in page-locked HOST memory (rt_render_host), the
+// plain kernel's stores cross NVLink / PCIe as 32-byte pieces (one 8-pixel tile row per warp).  Here a block owns
+// 32 x 4 pixels: every thread parks its pixel in shared memory, and after one barrier four threads issue the block's
+// 128-byte row segments (colour, depth and, when asked for, prim ids) as bulk asynchronous stores (cp.async.bulk
+// shared -> global, SASS UBLKCP): full 128-byte writes, no per-thread store instructions.  The block only waits until
+// the bulk engine has READ its shared memory (wait_group.read), not until the writes have landed on the far side of
+// the link: the grid's completion covers that.  W % 8 == 0.
 //   INOUT = false: fused clear, every pixel of the tile is produced here.
 //   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous colour and depth are
 //                  first fetched into the same shared-memory rows by bulk loads completing on an mbarrier; a pixel is
 //                  replaced only by a nearer hit, and the whole tile goes back.
-template <int KIND, bool INOUT>
+template <int KIND, bool INOUT, bool SECONDARY>
 __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
+  extern __shared__ float4 smemTris[];
   __shared__ __align__(128) uint32_t sColor[4][32];
   __shared__ __align__(128) float sDepth[4][32];
+  __shared__ __align__(128) uint32_t sPrim[4][32];
   __shared__ __align__(8) unsigned long long mbar;
+  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const FrameDev &f = a.frame;
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   const uint32_t x0 = blockIdx.x * 32u, v0 = centre_out(blockIdx.y, gridDim.y) * 4u;
   const uint32_t lx = warp * TILE_W + (lane & 7u), ly = lane >> 3;
   const uint32_t x = x0 + lx, v = v0 + ly;
   const uint32_t rowBytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
+  const bool wantPrim = a.prim != nullptr;
   if (INOUT) {
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
     if (threadIdx.x == 0) {
@@ -157,7 +163,8 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
 #pragma unroll
       for (uint32_t r = 0; r < 4u; ++r)
         if (v0 + r < f.rows_here && band_row(f, v0 + r) < f.H) ++rows;
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rows * 2u * rowBytes)
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                   "r"(rows * (wantPrim ? 3u : 2u) * rowBytes)
                    : "memory");
 #pragma unroll
       for (uint32_t r = 0; r < 4u; ++r) {
@@ -173,6 +180,11 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
                          (uint32_t)__cvta_generic_to_shared(&sDepth[r][0])),
                      "l"(a.t_in + px), "r"(rowBytes), "r"(bar)
                      : "memory");
+        if (wantPrim)
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                           (uint32_t)__cvta_generic_to_shared(&sPrim[r][0])),
+                       "l"(a.prim + px), "r"(rowBytes), "r"(bar)
+                       : "memory");
       }
     }
     uint32_t done = 0;
@@ -196,30 +208,41 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
       C4 col;
       float tNew = __int_as_float(0x7f800000);
       uint32_t prim;
-      if (intersection_color<KIND, false, false>(a.scene, f, nullptr, o, d, tPrev, col, tNew, prim, cnt) && !isinf(tNew)) {
+      if (intersection_color<KIND, false, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
+          !isinf(tNew)) {
         sColor[ly][lx] = color_pack_rgba(col);
         sDepth[ly][lx] = tNew;
+        if (wantPrim) sPrim[ly][lx] = prim;
       } else if (!INOUT) {  // fused FrameBuffer::clear (raytracing.hpp:16-19)
         sColor[ly][lx] = 0u;
         sDepth[ly][lx] = __int_as_float(0x7f800000);
+        if (wantPrim) sPrim[ly][lx] = RT_PRIM_MISS;
       }
     }
   }
+  // every thread orders ITS generic-proxy writes of the tile before the async proxy (the bulk stores below read the
+  // rows through it), then the barrier makes all of them visible to the four issuing threads
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
   if (threadIdx.x < 4u) {
     const uint32_t vr = v0 + threadIdx.x;
     const uint32_t row = vr < f.rows_here ? band_row(f, vr) : f.H;
     if (row < f.H && x0 < f.W) {
       const size_t px = (size_t)row * f.W + x0;
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> async proxy
       asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.color + px),
                    "r"((uint32_t)__cvta_generic_to_shared(&sColor[threadIdx.x][0])), "r"(rowBytes)
                    : "memory");
       asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.t_out + px),
                    "r"((uint32_t)__cvta_generic_to_shared(&sDepth[threadIdx.x][0])), "r"(rowBytes)
                    : "memory");
+      if (wantPrim)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.prim + px),
+                     "r"((uint32_t)__cvta_generic_to_shared(&sPrim[threadIdx.x][0])), "r"(rowBytes)
+                     : "memory");
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      // the shared-memory rows must stay valid until the bulk engine has read them; the writes themselves complete
+      // before the grid does
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
   }
 }
@@ -433,11 +456,18 @@ static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count,
     // between neighbouring tiles); the brute-force kernel stages its triangles per block and keeps 256.
     // a.tile_block (RT_TILE_BLOCK) overrides it for sweeps; only the plain primary-ray kernels have every shape.
     const int tb = a.tile_block;
-    if (KIND == KIND_BRUTE) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
-    if (!COUNT && !SECONDARY && a.stage_stores) {
+    if (KIND == KIND_BRUTE && !(!COUNT && a.stage_stores)) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
+    if (!COUNT && a.stage_stores) {
       dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 3u) / 4u);
-      if (a.stage_stores == 2) render_tiles_staged_kernel<KIND, true><<<grid, 128, 0, st>>>(a);
-      else render_tiles_staged_kernel<KIND, false><<<grid, 128, 0, st>>>(a);
+      if (a.stage_stores == 2) {
+        auto kern = render_tiles_staged_kernel<KIND, true, SECONDARY>;
+        if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        kern<<<grid, 128, smem, st>>>(a);
+      } else {
+        auto kern = render_tiles_staged_kernel<KIND, false, SECONDARY>;
+        if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        kern<<<grid, 128, smem, st>>>(a);
+      }
       return cudaGetLastError();
     }
     if (!COUNT && !SECONDARY) {

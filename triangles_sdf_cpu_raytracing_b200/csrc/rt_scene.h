@@ -61,11 +61,22 @@ struct alignas(16) TriDev {
   float4 v0, v1, v2;
 };
 
+// Brute-force scenes (every ray tests every triangle, no tree):
+//   BRUTE_ROOT_LEAF: what the reference itself does for a mesh of <= 8 triangles.  createNode makes node 0 a leaf
+//                    (triangles_raytracing.cpp:175-186: `end - start <= 24` indices and no split), and traverseNode(0)
+//                    on a leaf tests its triangles with NO box test and NO range check (:292-331).  Exact in every view.
+//   BRUTE_BOXED    : 9+ triangles, explicit RT_MESH_BRUTE only.  The ray is first culled against the mesh bounding box
+//                    with the reference's slab test and a triangle is accepted iff t <= tFar.  Equals the reference
+//                    wherever its answer does not depend on its tree (eye outside the mesh, cleared framebuffer), and
+//                    on cube.obj in every view; elsewhere it is one of many tree-dependent answers.
+constexpr uint32_t BRUTE_NONE = 0u, BRUTE_BOXED = 1u, BRUTE_ROOT_LEAF = 2u;
+constexpr uint32_t ROOT_LEAF_MAX_TRIS = 8u;  // triangles_raytracing.cpp:120-122,175-186
+
 struct MeshDev {
   const BvhNode *nodes;
   const TriDev *tris;
   uint32_t n_nodes, n_tris;
-  uint32_t brute;  // 1: no BVH, all triangles are tested from shared memory
+  uint32_t brute;  // BRUTE_*: no BVH, all triangles are tested from shared memory
   uint32_t literal_order;  // 1: tree imported from the reference: literal slab test + sort8 visit order
 };
 

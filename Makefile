@@ -10,7 +10,13 @@ OBJ   := $(CSRC)/build
 HOST  := $(PKG)/hostapi
 EXAMPLE := $(HOST)/example_frame_loop
 
-all: $(OUT) $(EXAMPLE)
+PEAKS := tools/peaks
+
+all: $(OUT) $(EXAMPLE) $(PEAKS)
+
+# measured roofs (FP32 with / without FMA, issue rate, cached-gather rates, dependent-load latency): run once per box
+$(PEAKS): tools/peaks.cu
+	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -o $@ $<
 
 $(OUT): $(OBJ)/rt_kernels_exact.o $(OBJ)/rt_kernels_fast.o $(OBJ)/rt_api.o $(OBJ)/bvh_builder.o $(OBJ)/bvh_gpu.o $(OBJ)/ingest.o $(OBJ)/rt_host.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart shared
@@ -50,4 +56,4 @@ $(OBJ)/bvh_builder.o: $(CSRC)/bvh_builder.cpp $(CSRC)/bvh_builder.h $(CSRC)/rt_s
 
 .PHONY: clean
 clean:
-	rm -rf $(OBJ) $(OUT) $(EXAMPLE)
+	rm -rf $(OBJ) $(OUT) $(EXAMPLE) $(PEAKS)

@@ -569,7 +569,8 @@ int render_on_stream(const rt_scene *scene, Replica &rep, const FrameDev &fd, ui
     bool staged = g_env_stage == 1 || store >= STORE_STAGED;
     // one process per GPU (rt_ipc_open): measured in round 1 (profiles/r1_multi/TABLE.txt) to pay when rank 0's inbound
     // NVLink is saturated, i.e. on 8 GPUs at 4K
-    if (!staged && (uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)
+    // (RT_STAGE_STORES=2 stages for every peer framebuffer, whatever the frame size and rank count: A/B measurements)
+    if (!staged && (g_env_stage == 2 || ((uint64_t)fd.W * fd.H >= (3ull << 20) && fd.band_count >= 8u)))
       staged = is_peer_pointer(color) && is_peer_pointer(t_out);
     a.stage_stores = staged ? (store == STORE_INOUT ? 2 : 1) : 0;
     if (staged && store < 0) g_staged_launches.fetch_add(1);  // counts the one-process-per-GPU path only

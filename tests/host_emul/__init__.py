@@ -122,14 +122,15 @@ class EmulScene:
         p = None if prim_of_permuted is None else np.ascontiguousarray(prim_of_permuted, np.uint32)
         return EmulScene(lib().emul_mesh_refbvh(_p(v), v.shape[0], _p(i), i.size, _p(nb), nb.shape[0], nb.shape[1], _p(p)))
 
-    def render(self, frame, color=None, t=None, want_prim=True):
-        """frame: the package's RtFrame (rt.make_frame).  -> (color [H,W] u32, t [H,W] f32, prim, counters dict)."""
+    def render(self, frame, color=None, t=None, want_prim=True, count=True):
+        """frame: the package's RtFrame (rt.make_frame).  -> (color [H,W] u32, t [H,W] f32, prim, counters dict).
+        count=False runs the kernels' plain flavour (no workload counters), the one the timed launches use."""
         H, W = frame.height, frame.width
         color = np.zeros((H, W), np.uint32) if color is None else np.ascontiguousarray(color, np.uint32).copy()
         t = np.full((H, W), np.inf, np.float32) if t is None else np.ascontiguousarray(t, np.float32).copy()
         prim = np.full((H, W), 0xFFFFFFFF, np.uint32) if want_prim else None
         cnt = np.zeros(9, np.uint64)
-        rc = lib().emul_render(self._h, C.byref(frame), _p(color), _p(t), _p(prim), _p(cnt))
+        rc = lib().emul_render(self._h, C.byref(frame), _p(color), _p(t), _p(prim), _p(cnt) if count else None)
         assert rc == 0
         return color, t, prim, dict(zip(COUNTER_NAMES, (int(x) for x in cnt)))
 

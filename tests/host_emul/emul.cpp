@@ -53,7 +53,7 @@ using std::min;
 #include "rt_shade.cuh"
 
 // shade_pixel of csrc/rt_kernels.cuh without the launch state: memory row `row` (0 = top), column x
-template <int KIND, bool SECONDARY>
+template <int KIND, bool SECONDARY, bool COUNT>
 static void pixel(const SceneDev &s, const FrameDev &f, const float4 *tris, uint32_t x, uint32_t row, uint32_t *color,
                   float *t, uint32_t *prim, Counters &cnt) {
   const size_t px = (size_t)row * f.W + x;
@@ -64,7 +64,7 @@ static void pixel(const SceneDev &s, const FrameDev &f, const float4 *tris, uint
   C4 col;
   float tNew;
   uint32_t pr;
-  if (intersection_color<KIND, true, SECONDARY>(s, f, tris, o, d, tPrev, col, tNew, pr, cnt) && !std::isinf(tNew)) {
+  if (intersection_color<KIND, COUNT, SECONDARY>(s, f, tris, o, d, tPrev, col, tNew, pr, cnt) && !std::isinf(tNew)) {
     t[px] = tNew;
     color[px] = color_pack_rgba(col);
     if (prim) prim[px] = pr;
@@ -75,14 +75,20 @@ static void pixel(const SceneDev &s, const FrameDev &f, const float4 *tris, uint
   }
 }
 
+// count = the kernels' COUNT flavour (workload counters; some paths, e.g. the octree's culled-child handling, differ)
 template <int KIND>
 static void frame(const SceneDev &s, const FrameDev &f, const float4 *tris, uint32_t *color, float *t, uint32_t *prim,
-                  Counters &cnt) {
+                  Counters &cnt, bool count) {
   const bool secondary = f.mode == RT_SHADE_LAMBERT && (f.shadows || f.reflections);
   for (uint32_t row = 0; row < f.H; ++row)
     for (uint32_t x = 0; x < f.W; ++x) {
-      if (secondary) pixel<KIND, true>(s, f, tris, x, row, color, t, prim, cnt);
-      else pixel<KIND, false>(s, f, tris, x, row, color, t, prim, cnt);
+      if (secondary) {
+        if (count) pixel<KIND, true, true>(s, f, tris, x, row, color, t, prim, cnt);
+        else pixel<KIND, true, false>(s, f, tris, x, row, color, t, prim, cnt);
+      } else {
+        if (count) pixel<KIND, false, true>(s, f, tris, x, row, color, t, prim, cnt);
+        else pixel<KIND, false, false>(s, f, tris, x, row, color, t, prim, cnt);
+      }
     }
 }
 
@@ -157,8 +163,24 @@ EmulScene *emul_octree(const void *nodes36, uint32_t n) {
     }
     e->link[i] = l;
   }
+  // k_oct_childmask of csrc/ingest.cu: inner link words learn which children are worth a visit
+  const bool masks = n < OCT_MASK_MAX_NODES;
+  if (masks) {
+    std::vector<uint32_t> masked(e->link);
+    for (uint32_t i = 0; i < n; ++i) {
+      uint32_t off;
+      std::memcpy(&off, raw + (size_t)i * 36 + 32, 4);
+      if (off == 0u || (unsigned long long)off + 7ull >= (unsigned long long)n) continue;
+      uint32_t mask = 0;
+      for (uint32_t c = 0; c < 8u; ++c)
+        if (e->link[off + c] != OCT_LEAF_CULLED) mask |= 1u << c;
+      masked[i] = off | (mask << 24);
+    }
+    e->link.swap(masked);
+  }
   e->dev.kind = RT_SCENE_OCTREE;
   OctreeDev &o = e->dev.oct;
+  o.has_mask = masks ? 1u : 0u;
   o.link = e->link.data();
   o.values = e->values.data();
   o.n_nodes = n;
@@ -353,11 +375,11 @@ int emul_render(const EmulScene *e, const rt_frame *fr, uint32_t *color, float *
   emul::Counters cnt = {};
   const SceneDev &s = e->dev;
   const float4 *tris = reinterpret_cast<const float4 *>(s.mesh.tris);
-  if (s.kind == RT_SCENE_GRID && s.grid.bricks) emul::frame<emul::KIND_GRID_BRICKS>(s, f, nullptr, color, t, prim, cnt);
-  else if (s.kind == RT_SCENE_GRID) emul::frame<emul::KIND_GRID>(s, f, nullptr, color, t, prim, cnt);
-  else if (s.kind == RT_SCENE_OCTREE) emul::frame<emul::KIND_OCTREE>(s, f, nullptr, color, t, prim, cnt);
-  else if (s.mesh.brute) emul::frame<emul::KIND_BRUTE>(s, f, tris, color, t, prim, cnt);
-  else emul::frame<emul::KIND_BVH>(s, f, nullptr, color, t, prim, cnt);
+  if (s.kind == RT_SCENE_GRID && s.grid.bricks) emul::frame<emul::KIND_GRID_BRICKS>(s, f, nullptr, color, t, prim, cnt, counters != nullptr);
+  else if (s.kind == RT_SCENE_GRID) emul::frame<emul::KIND_GRID>(s, f, nullptr, color, t, prim, cnt, counters != nullptr);
+  else if (s.kind == RT_SCENE_OCTREE) emul::frame<emul::KIND_OCTREE>(s, f, nullptr, color, t, prim, cnt, counters != nullptr);
+  else if (s.mesh.brute) emul::frame<emul::KIND_BRUTE>(s, f, tris, color, t, prim, cnt, counters != nullptr);
+  else emul::frame<emul::KIND_BVH>(s, f, nullptr, color, t, prim, cnt, counters != nullptr);
   if (counters) {
     const uint32_t v[9] = {cnt.rays, cnt.hits, cnt.grid_samples, cnt.oct_inner, cnt.oct_leaf, cnt.oct_leaf_samples,
                            cnt.bvh_inner, cnt.bvh_leaf, cnt.bvh_tris};

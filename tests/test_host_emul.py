@@ -58,6 +58,9 @@ def test_device_source_on_cpu_reproduces_the_golden_frames(key):
     for mode, name in ((rt.SHADE_NORMAL, "color_normal"), (rt.SHADE_LAMBERT, "color_lambert"), (rt.SHADE_COLOR, "color_color")):
         col, t, prim, _ = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=mode))
         assert util.same_bits(t, c["t"]), f"{key}: depth differs"
+        # the plain flavour (no workload counters: what the timed launches run; the octree filters its child lists there)
+        col2, t2, prim2, _ = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=mode), count=False)
+        assert util.same_bits(t2, t) and np.array_equal(col2, col) and np.array_equal(prim2, prim), f"{key}: flavours differ"
         if kind == "mesh":  # exact-t ties between two triangles: the winner depends on the tree
             assert (col != c[name]).sum() <= max(2, 1e-3 * W * H), f"{key}: {name} differs beyond tie pixels"
         else:
@@ -66,6 +69,8 @@ def test_device_source_on_cpu_reproduces_the_golden_frames(key):
         f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=rt.SHADE_LAMBERT, shadows=True,
                           reflections=True, plane_y=float(c["plane_y"]))
         col, t, _, _ = s.render(f)
+        col2, t2, _, _ = s.render(f, count=False)
+        assert util.same_bits(t2, t) and np.array_equal(col2, col), f"{key}: plane + secondary rays, flavours differ"
         assert util.same_bits(t, c["t_full"]), f"{key}: plane + secondary rays, depth"
         if kind == "mesh" and c["scene"] != "cube":
             # a secondary ray starts on the surface: whether a triangle behind it is tested depends on the tree (T6)
@@ -87,6 +92,8 @@ def test_device_source_on_cpu_vs_oracle_seeded_cameras_sdf(name, n_cams):
         f = rt.make_frame(pos, vinv, pinv, W, H, mode=mode, shadows=plane, reflections=plane,
                           plane_y=-1.0 if plane else None)
         col, t, _, cnt = s.render(f)
+        col2, t2, _, _ = s.render(f, count=False)  # the plain flavour the timed launches run
+        assert util.same_bits(t2, t) and np.array_equal(col2, col), f"{name} camera {k}: counting and plain flavours differ"
         sc = ps.with_plane(-1.0) if plane else ps
         pc, pt, _, pcnt = sc.render(pos, vinv, pinv, W, H, mode=mode, shadows=plane, reflections=plane, want_counters=True)
         assert util.same_bits(t, pt), f"{name} camera {k}: depth differs on {(util.bits(t) != util.bits(pt)).sum()} pixels"
@@ -414,6 +421,8 @@ def test_random_octrees_vs_oracle(seed):
     pinv = rt.host_projection(W, H)[1]
     for k, pos, vinv in seeded_cameras(10, seed=seed):
         col, t, _, cnt = s.render(rt.make_frame(pos, vinv, pinv, W, H))
+        col2, t2, _, _ = s.render(rt.make_frame(pos, vinv, pinv, W, H), count=False)
+        assert util.same_bits(t2, t) and np.array_equal(col2, col), "counting and plain flavours differ"
         pc, pt, _, pcnt = ps.render(pos, vinv, pinv, W, H, want_counters=True)
         assert util.same_bits(t, pt) and np.array_equal(col, pc), f"seed {seed} camera {k} ({nodes.shape[0]} nodes)"
         for cn, pn in COUNTERS["octree"].items():

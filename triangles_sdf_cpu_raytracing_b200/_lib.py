@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+# RT_B200_LIB selects another build of the same library (kernel experiments, tools/build_variants.sh)
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 RT_OK = 0
 SHADE_NORMAL, SHADE_LAMBERT, SHADE_COLOR = 0, 1, 2

@@ -80,6 +80,24 @@ __global__ void k_oct_frontier(const uint32_t *rawLink, uint32_t n, const uint32
   }
 }
 
+// Inner nodes learn which of their children are leaves that intersectLeaf rejects from their values alone: the
+// traversal then skips those without loading their records.  Runs after the walk above has validated every reachable
+// offset; nodes the walk never reached may hold anything, so the range is checked here too.
+__global__ void k_oct_childmask(const uint32_t *rawLink, const uint32_t *link, uint32_t n, uint32_t *out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t off = rawLink[i];
+  uint32_t l = link[i];
+  if (off != 0u && (unsigned long long)off + 7ull < (unsigned long long)n) {
+    uint32_t mask = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 8u; ++c)
+      if (link[off + c] != OCT_LEAF_CULLED) mask |= 1u << c;
+    l = off | (mask << 24);
+  }
+  out[i] = l;
+}
+
 __global__ void k_grid_bricks(const float *lin, uint32_t sx, uint32_t sy, uint32_t sz, uint32_t nby, uint32_t nbz,
                               size_t total, float *out) {
   const size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -118,7 +136,8 @@ struct Tmp {
 }  // namespace
 
 int ingest_octree_device(const void *nodes36, uint32_t n, uint32_t **linkOut, float4 **valuesOut, uint32_t *depthOut,
-                         float *ms, std::string &err) {
+                         uint32_t *hasMaskOut, float *ms, std::string &err) {
+  *hasMaskOut = 0;
   *linkOut = nullptr;
   *valuesOut = nullptr;
   Tmp tmp;
@@ -182,6 +201,16 @@ int ingest_octree_device(const void *nodes36, uint32_t n, uint32_t **linkOut, fl
     const uint32_t zero = 0;
     ce = cudaMemcpy(&st->count[cur], &zero, 4, cudaMemcpyHostToDevice);
     cur ^= 1;
+  }
+  if (ce == cudaSuccess && n < OCT_MASK_MAX_NODES) {
+    uint32_t *masked = nullptr;
+    ce = cudaMalloc(&masked, std::max<size_t>((size_t)n * 4, 16));
+    if (ce == cudaSuccess) {
+      k_oct_childmask<<<(n + 255) / 256, 256>>>(rawLink, link, n, masked);
+      cudaFree(link);  // stream-ordered: the kernel above has been enqueued before the free takes effect
+      link = masked;
+      *hasMaskOut = 1;
+    }
   }
   cudaEventRecord(e1);
   if (ce == cudaSuccess) ce = cudaDeviceSynchronize();

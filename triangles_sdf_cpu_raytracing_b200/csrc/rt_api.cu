@@ -307,10 +307,10 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
   int rc = scene_begin(out, s);
   if (rc) return rc;
   DeviceGuard dg(s->reps[0]->device);
-  uint32_t *link = nullptr, depth = 0;
+  uint32_t *link = nullptr, depth = 0, has_mask = 0;
   float4 *vals = nullptr;
   std::string ierr;
-  const int irc = ingest_octree_device(nodes36, n_nodes, &link, &vals, &depth, &s->build_ms, ierr);
+  const int irc = ingest_octree_device(nodes36, n_nodes, &link, &vals, &depth, &has_mask, &s->build_ms, ierr);
   if (irc != INGEST_OK) {
     scene_free(s);
     return fail(irc == INGEST_INVALID ? RT_ERR_INVALID : RT_ERR_CUDA, ierr);
@@ -324,6 +324,7 @@ int rt_scene_create_octree(const void *nodes36, uint32_t n_nodes, rt_scene **out
   oc.n_nodes = n_nodes;
   oc.depth = depth;
   oc.root_inner = depth > 0 ? 1u : 0u;
+  oc.has_mask = has_mask;
   oc.link = link;
   oc.values = vals;
   rc = scene_finish(s, out);
@@ -798,7 +799,11 @@ int render_device_multi(const rt_scene *s, Replica &owner, const FrameDev &fd, u
     if (rc) return rc;
   }
   const bool inout = !fd.clear && t_in != nullptr;
-  const bool can_stage = staged_kernel_available(fd, nullptr) && (fd.clear || inout) && g_env_stage != 0 &&
+  // Staged 128-byte stores pay when the owner's NVLink ingress is the limit (8 GPUs on a >= 3 Mpixel frame: 4K grid
+  // 0.139 -> 0.096 ms in round 1); below that the plain kernel's 32-byte tile rows are faster (2 GPUs, 4K grid: 0.221 vs
+  // 0.247 ms, profiles/r2_multi/).  The in/out contract always stages: its bulk loads replace per-thread remote reads.
+  const bool worth = g_env_stage == 2 || g_env_stage == 1 || inout || (n >= 8u && (uint64_t)fd.W * fd.H >= (3ull << 20));
+  const bool can_stage = worth && staged_kernel_available(fd, nullptr) && (fd.clear || inout) && g_env_stage != 0 &&
                          reinterpret_cast<uintptr_t>(color) % 16u == 0 && reinterpret_cast<uintptr_t>(t_out) % 16u == 0 &&
                          reinterpret_cast<uintptr_t>(prim) % 16u == 0 && (!inout || t_in == t_out);
   {

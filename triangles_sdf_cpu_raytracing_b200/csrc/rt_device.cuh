@@ -235,6 +235,8 @@ __device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, floa
   V3 p = along(o, d, t);
   p.x = std_max(p.x, -1.0f); p.y = std_max(p.y, -1.0f); p.z = std_max(p.z, -1.0f);
   p.x = std_min(p.x, 1.0f); p.y = std_min(p.y, 1.0f); p.z = std_min(p.z, 1.0f);
+  // (the six bound tests as one `max(|x|, |y|, |z|) <= 1` and a cell index recomputed after the loop were measured:
+  // 1080p 0.112 -> 0.139 ms, 513^3 4K 0.366 -> 0.395 ms; the compiler's loop with the six compares is the better one)
   while (p.x <= 1.0f && p.y <= 1.0f && p.z <= 1.0f && p.x >= -1.0f && p.y >= -1.0f && p.z >= -1.0f) {
     uint32_t cell;
     float sd = grid_sdf<BRICKS, COUNT>(g, p, cell, cnt);
@@ -249,6 +251,13 @@ __device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, floa
   }
   if (r.hitten) r.normal = grid_normal<BRICKS, COUNT>(g, p, cnt);
   return r;
+}
+
+// compare-exchange of two packed sort keys (octree crossing order, BVH child order)
+__device__ __forceinline__ void key_cswap(uint32_t &a, uint32_t &b) {
+  const uint32_t lo = min(a, b), hi = max(a, b);
+  a = lo;
+  b = hi;
 }
 
 // =============================================================================================================
@@ -385,8 +394,25 @@ __device__ __forceinline__ void oct_child_entries(V3 bmin, float ext, V3 o, V3 i
 // strictly increasing (T_in-side first, then the M_a of each crossing), so sort8 would list them in this order.
 // Any exact tie (two equal centre distances, or one equal to a window end) makes the closed form ambiguous: the
 // caller then falls back to the literal 8-box test + sort8.  Returns false when the fallback is needed.
+// (experiment switches, fixed by measurement: profiles/r2_octree_variants.txt)
+#ifndef RT_OCT_KEYS
+#define RT_OCT_KEYS 1     // crossings ordered through packed 32-bit keys (else a 3-comparator network on (t, axis) pairs)
+#endif
+#ifndef RT_OCT_MASK
+#define RT_OCT_MASK 2     // kept-children mask: 0 unused, 1 tested when a child is taken, 2 applied when the list is built
+#endif
+#ifndef RT_OCT_STACK64
+#define RT_OCT_STACK64 0  // one 64-bit stack entry per level (else two 32-bit arrays); measured slower (+1.3 %)
+#endif
+#ifndef RT_OCT_CFWORD
+#define RT_OCT_CFWORD 0   // 32-bit arrays: "closed-form list" flag kept in bit 31 of the saved list (else a per-level bit mask)
+#endif
+
+// keep: bit c set = child c is worth a visit (everything else is a leaf intersectLeaf rejects from its values alone);
+// FILTER: drop the others from the list right here (the kernels that count visits keep them and skip them one by one)
+template <bool FILTER>
 __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 inv, uint32_t nearMask, float tNear,
-                                                  float tFar, uint32_t &w) {
+                                                  float tFar, uint32_t keep, uint32_t &w) {
   const float h = ext * 0.5f;
   const float ax0 = (bmin.x - o.x) * inv.x, ax1 = (bmin.x + h - o.x) * inv.x, ax2 = (bmin.x + ext - o.x) * inv.x;
   const float ay0 = (bmin.y - o.y) * inv.y, ay1 = (bmin.y + h - o.y) * inv.y, ay2 = (bmin.y + ext - o.y) * inv.y;
@@ -396,13 +422,24 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
   // crossings strictly inside the window; equal centre distances only matter when both are inside it (two
   // crossings before T_in just mean "far half on both axes", e.g. a camera on a coordinate axis at the root)
   const bool ex = tIn < ax1 && ax1 < tOut, ey = tIn < ay1 && ay1 < tOut, ez = tIn < az1 && az1 < tOut;
+#if RT_OCT_KEYS
+  // The crossings are ordered through ONE 32-bit key each: the distance's bit pattern (positive: tIn >= tNear > 0, so
+  // the patterns order like the floats) with its two low mantissa bits replaced by the axis (0 -> x, 1 -> y, 2 -> z).
+  // Two crossings whose distances agree in the upper 30 bits (equal, or within 3 ulp) count as a tie and take the
+  // literal path, so the order taken here is always the exact one.  Crossings outside the window sort last.
+  uint32_t k0 = ex ? (__float_as_uint(ax1) & ~3u) : 0xFFFFFFFFu;
+  uint32_t k1 = ey ? ((__float_as_uint(ay1) & ~3u) | 1u) : 0xFFFFFFFFu;
+  uint32_t k2 = ez ? ((__float_as_uint(az1) & ~3u) | 2u) : 0xFFFFFFFFu;
+  key_cswap(k0, k1); key_cswap(k1, k2); key_cswap(k0, k1);
+  const bool tie = ((k0 ^ k1) < 4u && k1 != 0xFFFFFFFFu) || ((k1 ^ k2) < 4u && k2 != 0xFFFFFFFFu) || ax1 == tIn ||
+                   ay1 == tIn || az1 == tIn || ax1 == tOut || ay1 == tOut || az1 == tOut;
+  if (tie) return false;
+  const bool v0 = k0 != 0xFFFFFFFFu, v1 = k1 != 0xFFFFFFFFu, v2 = k2 != 0xFFFFFFFFu;
+  const uint32_t m0 = 4u >> (k0 & 3u), m1 = 4u >> (k1 & 3u), m2 = 4u >> (k2 & 3u);
+#else
   const bool tie = (ex && ey && ax1 == ay1) || (ex && ez && ax1 == az1) || (ey && ez && ay1 == az1) || ax1 == tIn ||
                    ay1 == tIn || az1 == tIn || ax1 == tOut || ay1 == tOut || az1 == tOut;
   if (tie) return false;
-  w = 0;
-  if (tIn > tOut) return true;  // the ray misses this node's box inside [tNear, tFar]: no child can be hit
-  // child at the window start, in ray order (bit set = far half), x -> 4, y -> 2, z -> 1 as in divide_box_8
-  uint32_t k = (ax1 < tIn ? 4u : 0u) | (ay1 < tIn ? 2u : 0u) | (az1 < tIn ? 1u : 0u);
   const float INF = __int_as_float(0x7f800000);
   float k0 = ex ? ax1 : INF, k1 = ey ? ay1 : INF, k2 = ez ? az1 : INF;
   uint32_t m0 = 4u, m1 = 2u, m2 = 1u;
@@ -413,11 +450,25 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
   }
   RT_CS3(k0, k1, m0, m1) RT_CS3(k1, k2, m1, m2) RT_CS3(k0, k1, m0, m1)
 #undef RT_CS3
+  const bool v0 = k0 < INF, v1 = k1 < INF, v2 = k2 < INF;
+#endif
+  w = 0;
+  if (tIn > tOut) return true;  // the ray misses this node's box inside [tNear, tFar]: no child can be hit
+  // child at the window start, in ray order (bit set = far half), x -> 4, y -> 2, z -> 1 as in divide_box_8
+  uint32_t k = (ax1 < tIn ? 4u : 0u) | (ay1 < tIn ? 2u : 0u) | (az1 < tIn ? 1u : 0u);
   k ^= nearMask;  // ray order -> spatial child id
-  w = 8u | k;
-  if (k0 < INF) { k ^= m0; w |= (8u | k) << 4; }
-  if (k1 < INF) { k ^= m1; w |= (8u | k) << 8; }
-  if (k2 < INF) { k ^= m2; w |= (8u | k) << 12; }
+  if (FILTER) {
+    uint32_t sh = 0;
+    if ((keep >> k) & 1u) { w = 8u | k; sh = 4u; }
+    if (v0) { k ^= m0; if ((keep >> k) & 1u) { w |= (8u | k) << sh; sh += 4u; } }
+    if (v1) { k ^= m1; if ((keep >> k) & 1u) { w |= (8u | k) << sh; sh += 4u; } }
+    if (v2) { k ^= m2; if ((keep >> k) & 1u) { w |= (8u | k) << sh; } }
+  } else {
+    w = 8u | k;
+    if (v0) { k ^= m0; w |= (8u | k) << 4; }
+    if (v1) { k ^= m1; w |= (8u | k) << 8; }
+    if (v2) { k ^= m2; w |= (8u | k) << 12; }
+  }
   return true;
 }
 
@@ -425,15 +476,17 @@ __device__ __forceinline__ bool oct_children_fast(V3 bmin, float ext, V3 o, V3 i
 // The reference recursion returns as soon as ANY leaf reports a hit (the first hitting child ends every
 // enclosing loop, :188-197), so `hit.t > t` is never evaluated with a hit in hand: the visit rule is just
 // t > 0 in sort8 order.  Per level we keep one word: the not-yet-visited children in visit order, 4 bits each
-// (bit 3 = valid), and the node's childrenOffset.  Child boxes come from integer (level, i, j, k): the dyadic
+// (bit 3 = valid), and the node's link word.  Child boxes come from integer (level, i, j, k): the dyadic
 // subdivision of [-1,1] that divide_box_8 (ray_pack.ispc:220-239) computes is exact.
 // ordered list of the children of the inner node with box (bmin, ext) that the ray visits: up to 8 nibbles,
 // first to visit in the low nibble, bit 3 = valid, bits 0..2 = child id
+template <bool FILTER>
 __device__ __forceinline__ uint32_t oct_children(V3 bmin, float ext, V3 o, V3 inv, bool finiteInv, bool fastOk,
-                                                 uint32_t nearMask, float tNear, float tFar, bool &closedForm) {
+                                                 uint32_t nearMask, float tNear, float tFar, uint32_t keep,
+                                                 bool &closedForm) {
   uint32_t w = 0;
   // closedForm: the list came from the closed form, so every child in it passed a NaN-free slab test
-  closedForm = fastOk && oct_children_fast(bmin, ext, o, inv, nearMask, tNear, tFar, w);
+  closedForm = fastOk && oct_children_fast<FILTER>(bmin, ext, o, inv, nearMask, tNear, tFar, keep, w);
   if (closedForm) return w;
   // literal path: axis-parallel rays, tNear <= 0, exact ties
   float ts[8];
@@ -444,7 +497,7 @@ __device__ __forceinline__ uint32_t oct_children(V3 bmin, float ext, V3 o, V3 in
   w = 0;
 #pragma unroll
   for (int i = 7; i >= 0; --i)
-    if (ts[i] > 0) w = (w << 4) | 8u | ch[i];
+    if (ts[i] > 0 && (!FILTER || ((keep >> ch[i]) & 1u))) w = (w << 4) | 8u | ch[i];
   return w;
 }
 
@@ -469,18 +522,32 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
   } else {
     // Iterate the children of the CURRENT inner node from registers; only stepping into an inner child saves
     // the parent's state (leaf children, the majority of visits, never touch the stack).
-    uint32_t pend[OCT_MAX_DEPTH + 1];  // per level: the parent's not-yet-visited children ...
-    uint32_t base[OCT_MAX_DEPTH + 1];  // ... and its childrenOffset
+#if RT_OCT_STACK64
+    // One 64-bit entry per level: low word = the parent's not-yet-visited children (<= 7 nibbles once a child has been
+    // taken) with bit 31 = "that list is a closed-form one", high word = the parent's link word.
+    unsigned long long stack[OCT_MAX_DEPTH + 1];
+#else
+    uint32_t pend[OCT_MAX_DEPTH + 1], base[OCT_MAX_DEPTH + 1];
+#if !RT_OCT_CFWORD
+    uint32_t closedMask = 0;  // bit l: the child list of the level-l node on the path is a closed-form one
+#endif
+#endif
     int level = 0;                     // depth of the current inner node
     V3 bmin = mk3(-1.0f, -1.0f, -1.0f);  // its box: dyadic, so parent/child corners are exact sums
     float ext = 2.0f, invExt = 0.5f;   // 1/ext: both powers of two, kept exact by doubling / halving
     unsigned long long path = 0;       // 3 bits per level: child ids on the way down (for stepping back up)
-    uint32_t closedMask = 0;           // bit l: the child list of the level-l node on the path is a closed-form one
-    uint32_t cbase = rootLink;
+    const bool hasMask = RT_OCT_MASK != 0 && oc.has_mask != 0u;
+    const uint32_t offMask = oc.has_mask ? OCT_OFFSET_MASK : 0xFFFFFFFFu;
+    // the kernels that count visits take the culled children one by one (each is a leaf visit of the reference)
+    constexpr bool FILTER = RT_OCT_MASK == 2 && !COUNT;
+    uint32_t lw = rootLink;            // link word of the current node: childrenOffset (| kept-children mask << 24)
     if (COUNT) cnt.oct_inner++;
-    bool cf;
-    uint32_t w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+    bool cf;  // the current node's child list came from the closed form: its children passed a NaN-free slab test
+    uint32_t w = oct_children<FILTER>(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar,
+                                      hasMask ? lw >> 24 : 0xFFu, cf);
+#if !RT_OCT_STACK64 && !RT_OCT_CFWORD
     closedMask = cf ? 1u : 0u;
+#endif
     // (A "while-while" form, all lanes walking to their next surface leaf before any of them marches, was measured
     // and rejected: octree6 4K 0.73 -> 0.75 ms, depth-8 stand-in 1.16 -> 1.34 ms; profiles/r1_tune.txt.)
     for (;;) {
@@ -488,8 +555,20 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
         // ---- back to the parent
         if (level == 0) break;
         --level;
+#if RT_OCT_STACK64
+        const unsigned long long e = stack[level];
+        w = (uint32_t)e;
+        lw = (uint32_t)(e >> 32);
+        cf = (w >> 31) != 0u;
+        w &= 0x7FFFFFFFu;
+#else
         w = pend[level];
-        cbase = base[level];
+        lw = base[level];
+#if RT_OCT_CFWORD
+        cf = (w >> 31) != 0u;
+        w &= 0x7FFFFFFFu;
+#endif
+#endif
         const uint32_t id = (uint32_t)path & 7u;
         path >>= 3;
         bmin = mk3(bmin.x - ((id & 4u) ? ext : 0.0f), bmin.y - ((id & 2u) ? ext : 0.0f), bmin.z - ((id & 1u) ? ext : 0.0f));
@@ -499,16 +578,26 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
       }
       const uint32_t id = w & 7u;
       w >>= 4;
-      const uint32_t child = cbase + id;
+      // a child that is a leaf intersectLeaf rejects from its values alone (octree_raytracing.cpp:128-135) is known from
+      // the parent's link word: visited (it counts as a leaf visit) without touching its record
+      if (!FILTER && hasMask && !((lw >> (24u + id)) & 1u)) {
+        if (COUNT) cnt.oct_leaf++;
+        continue;
+      }
+      const uint32_t child = (lw & offMask) + id;
       const uint32_t link = __ldg(oc.link + child);
       const float h = ext * 0.5f;
-      const V3 cmin = mk3(bmin.x + ((id & 4u) ? h : 0.0f), bmin.y + ((id & 2u) ? h : 0.0f), bmin.z + ((id & 1u) ? h : 0.0f));
       if (link == OCT_LEAF_SURFACE || link == OCT_LEAF_CULLED) {
         if (COUNT) cnt.oct_leaf++;
         if (link == OCT_LEAF_SURFACE) {
+          const V3 cmin = mk3(bmin.x + ((id & 4u) ? h : 0.0f), bmin.y + ((id & 2u) ? h : 0.0f), bmin.z + ((id & 1u) ? h : 0.0f));
           const float ih = invExt * 2.0f;
-          if (oct_leaf<COUNT>(oc, child, cmin, h, ih, o, d, inv, tNear, tFar, ((closedMask >> level) & 1u) != 0u, r,
-                              pHit, cnt)) {
+#if RT_OCT_STACK64 || RT_OCT_CFWORD
+          const bool known = cf;
+#else
+          const bool known = ((closedMask >> level) & 1u) != 0u;
+#endif
+          if (oct_leaf<COUNT>(oc, child, cmin, h, ih, o, d, inv, tNear, tFar, known, r, pHit, cnt)) {
             hitMin = cmin;
             hitInvExt = ih;
             break;  // the first leaf that reports a hit ends the whole descent (octree_raytracing.cpp:188-197)
@@ -516,16 +605,23 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
         }
       } else {
         if (COUNT) cnt.oct_inner++;
-        pend[level] = w;
-        base[level] = cbase;
+#if RT_OCT_STACK64
+        stack[level] = ((unsigned long long)lw << 32) | (unsigned long long)(w | (cf ? 0x80000000u : 0u));
+#else
+        pend[level] = RT_OCT_CFWORD ? (w | (cf ? 0x80000000u : 0u)) : w;
+        base[level] = lw;
+#endif
         ++level;
         path = (path << 3) | id;
-        bmin = cmin;
+        bmin = mk3(bmin.x + ((id & 4u) ? h : 0.0f), bmin.y + ((id & 2u) ? h : 0.0f), bmin.z + ((id & 1u) ? h : 0.0f));
         ext = h;
         invExt *= 2.0f;
-        cbase = link;
-        w = oct_children(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+        lw = link;
+        w = oct_children<FILTER>(bmin, ext, o, inv, finiteInv, fastOk, nearMask, tNear, tFar,
+                                 hasMask ? lw >> 24 : 0xFFu, cf);
+#if !RT_OCT_STACK64 && !RT_OCT_CFWORD
         closedMask = (closedMask & ~(1u << level)) | (cf ? (1u << level) : 0u);
+#endif
       }
     }
   }
@@ -579,7 +675,7 @@ __device__ __forceinline__ void oct_walk_begin(OctWalk &s, const OctreeDev &oc, 
   s.cbase = __ldg(oc.link);
   if (COUNT) cnt.oct_inner++;
   bool cf;
-  s.w = oct_children(s.bmin, s.ext, o, s.inv, finiteInv, fastOk, nearMask, tNear, tFar, cf);
+  s.w = oct_children<false>(s.bmin, s.ext, o, s.inv, finiteInv, fastOk, nearMask, tNear, tFar, 0xFFu, cf);
   s.closedMask = cf ? 1u : 0u;
 }
 
@@ -601,7 +697,7 @@ __device__ __forceinline__ int oct_walk_step(OctWalk &s, const OctreeDev &oc, V3
   }
   const uint32_t id = s.w & 7u;
   s.w >>= 4;
-  const uint32_t child = s.cbase + id;
+  const uint32_t child = (s.cbase & (oc.has_mask ? OCT_OFFSET_MASK : 0xFFFFFFFFu)) + id;
   const uint32_t link = __ldg(oc.link + child);
   const float h = s.ext * 0.5f;
   const V3 cmin = mk3(s.bmin.x + ((id & 4u) ? h : 0.0f), s.bmin.y + ((id & 2u) ? h : 0.0f), s.bmin.z + ((id & 1u) ? h : 0.0f));
@@ -625,8 +721,8 @@ __device__ __forceinline__ int oct_walk_step(OctWalk &s, const OctreeDev &oc, V3
   s.invExt *= 2.0f;
   s.cbase = link;
   bool cf;
-  s.w = oct_children(s.bmin, s.ext, o, s.inv, (s.flags & 1u) != 0u, (s.flags & 2u) != 0u, (s.flags >> 4) & 7u, tNear,
-                     s.tFar, cf);
+  s.w = oct_children<false>(s.bmin, s.ext, o, s.inv, (s.flags & 1u) != 0u, (s.flags & 2u) != 0u, (s.flags >> 4) & 7u,
+                            tNear, s.tFar, 0xFFu, cf);
   s.closedMask = (s.closedMask & ~(1u << s.level)) | (cf ? (1u << s.level) : 0u);
   return OCT_WALK_CONTINUE;
 }
@@ -664,11 +760,6 @@ __device__ __forceinline__ bool oct_walk_leaf(const OctWalk &s, const OctreeDev 
 //    ties between triangles can resolve differently, and those already depend on the tree.
 // Trees imported from the reference (rt_scene_create_mesh_bvh8) keep the literal slab test + sort8 network so
 // that their visit order, and with it every tie, is the reference's own.
-__device__ __forceinline__ void key_cswap(uint32_t &a, uint32_t &b) {
-  const uint32_t lo = min(a, b), hi = max(a, b);
-  a = lo;
-  b = hi;
-}
 
 template <bool COUNT>
 __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {

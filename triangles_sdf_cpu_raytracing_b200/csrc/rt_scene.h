@@ -27,9 +27,13 @@ struct GridDev {
 //   link == OCT_LEAF_CULLED : leaf that intersectLeaf rejects from its values alone (isEmpty
 //                             octree_raytracing.hpp:12-17, or all >= 1e-4 octree_raytracing.cpp:132-135)
 //   link == OCT_LEAF_SURFACE: leaf that must be marched
-//   otherwise               : childrenOffset of an inner node
+//   otherwise               : inner node: childrenOffset, and when has_mask (fewer than 2^24 nodes) bits 24..31 say which
+//                             of its 8 children are worth a visit (bit c clear: child c is an OCT_LEAF_CULLED leaf; the
+//                             traversal counts it as visited without loading its record)
 constexpr uint32_t OCT_LEAF_SURFACE = 0u;
 constexpr uint32_t OCT_LEAF_CULLED = 0xFFFFFFFFu;
+constexpr uint32_t OCT_OFFSET_MASK = 0x00FFFFFFu;
+constexpr uint32_t OCT_MASK_MAX_NODES = 1u << 24;  // offsets must leave the top byte free (offset + 7 < n_nodes)
 constexpr int OCT_MAX_DEPTH = 21;  // child boxes stay exactly representable; 3 path bits per level in 64
 struct OctreeDev {
   const uint32_t *link;
@@ -37,6 +41,7 @@ struct OctreeDev {
   uint32_t n_nodes;
   uint32_t depth;
   uint32_t root_inner;  // 1: node 0 has children (always, except for a one-node file)
+  uint32_t has_mask;    // 1: inner link words carry the kept-children mask in bits 24..31
 };
 
 // ---- triangle mesh ------------------------------------------------------------------------------------

@@ -171,3 +171,34 @@ s = util.cuda_scene(g, "example_grid")
 assert len(s.replicas()) == 1
 print("all ok")
 """, env={"RT_MULTI_BAND_ROWS": band_rows})
+
+
+def test_cpp_renderer_draw_on_every_listed_device(tmp_path):
+    """hostapi/example_frame_loop (the viewer's frame loop, reference class names) with RT_DEVICES listing every GPU:
+    Renderer::draw -> one rt_render_host call -> the reference's frames, pageable and pinned FrameBuffer."""
+    import numpy as np
+    from tests import util
+    n = _n_gpus()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs (gpurun --gpus 2)")
+    exe = os.path.join(ROOT, "triangles_sdf_cpu_raytracing_b200", "hostapi", "example_frame_loop")
+    if not os.path.exists(exe):
+        pytest.skip("example_frame_loop has not been built (make)")
+    g = util.Golden()
+    c = g.case("example_grid|default|160x90")
+    v = g.scene_arrays("example_grid")["values"]
+    with open(tmp_path / "g.grid", "wb") as f:
+        f.write(np.array(v.shape, np.uint32).tobytes())
+        f.write(np.ascontiguousarray(v, np.float32).tobytes())
+    env = dict(os.environ, RT_DEVICES=",".join(str(d) for d in range(n)))
+    for extra, look, want_c, want_t in (([], ("normal", "0"), c["color_normal"], c["t"]),
+                                        (["0", "pinned"], ("normal", "0"), c["color_normal"], c["t"]),
+                                        (["0", "pinned"], ("lambert", "1"), c["color_full"], c["t_full"])):
+        out = tmp_path / "o.raw"
+        p = subprocess.run([exe, str(tmp_path / "g.grid"), "160", "90", *look, str(out), *extra], env=env,
+                           capture_output=True, text=True, timeout=120)
+        assert p.returncode == 0, p.stderr
+        raw = np.fromfile(out, dtype=np.uint8)
+        color = raw[:4 * 160 * 90].view(np.uint32).reshape(90, 160)
+        t = raw[4 * 160 * 90:].view(np.float32).reshape(90, 160)
+        assert util.same_bits(t, want_t) and np.array_equal(color, want_c), (extra, look)

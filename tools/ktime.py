@@ -23,6 +23,7 @@ ap.add_argument("--sched", default="auto")
 ap.add_argument("--reps", type=int, default=30)
 ap.add_argument("--math", default="exact")
 ap.add_argument("--check", action="store_true")
+ap.add_argument("--bands", type=int, default=1, help="time rank 0's share of a frame split into 8-row bands over this many GPUs")
 args = ap.parse_args()
 rt.set_math_mode(rt.MATH_FAST if args.math == "fast" else rt.MATH_EXACT)
 rt.set_sched_mode({"auto": rt.SCHED_AUTO, "tiles": rt.SCHED_TILES, "persistent": rt.SCHED_PERSISTENT, "compact": rt.SCHED_COMPACT}[args.sched])
@@ -35,7 +36,8 @@ for name in args.scenes:
     lk, plane_y = bench.look_kwargs(look, bench.model_plane_y(arrays))
     mode = rt.SHADE_LAMBERT if look == "default" else rt.SHADE_NORMAL
     s = util.cuda_scene(g, scene_name)
-    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=mode, plane_y=plane_y, clear=True, **lk)
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, mode=mode, plane_y=plane_y, clear=True,
+                      bands=(8, args.bands, 0) if args.bands > 1 else None, **lk)
     color = torch.zeros(W * H, dtype=torch.int32, device=dev)
     t = torch.zeros(W * H, dtype=torch.float32, device=dev)
     st = torch.cuda.current_stream()
@@ -61,6 +63,6 @@ for name in args.scenes:
         ev.append((a, b))
     torch.cuda.synchronize()
     ms = [a.elapsed_time(b) for a, b in ev]
-    print(f"{tag:28s} {name:28s} sched {args.sched:10s} mean {np.mean(ms):8.4f} ms  min {np.min(ms):8.4f}  {W * H / np.mean(ms) / 1e3:9.0f} Mrays/s{ok}",
+    print(f"{tag:28s} {name:28s} 1/{args.bands} sched {args.sched:10s} mean {np.mean(ms):8.4f} ms  min {np.min(ms):8.4f}  {W * H / args.bands / np.mean(ms) / 1e3:9.0f} Mrays/s{ok}",
           flush=True)
     s.destroy()

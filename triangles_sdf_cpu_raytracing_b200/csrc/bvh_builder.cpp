@@ -49,7 +49,11 @@ struct Builder {
   std::vector<Prim> prims;
   std::vector<BinNode> bin;
 
-  int build(uint32_t first, uint32_t count) {
+  // depth: recursion level.  A SAH split can peel one primitive off a skewed range at a time; past MAX_SAH_DEPTH levels
+  // the range is halved by count instead, so the recursion (and the traversal stack the tree needs) stays bounded by
+  // MAX_SAH_DEPTH + log2(n) whatever the input looks like.
+  static constexpr int MAX_SAH_DEPTH = 48;
+  int build(uint32_t first, uint32_t count, int depth = 0) {
     int idx = (int)bin.size();
     bin.emplace_back();
     Box box, cbox;
@@ -66,7 +70,7 @@ struct Builder {
     // binned SAH over the three axes
     int bestAxis = -1, bestBin = -1;
     float bestCost = INF;
-    for (int a = 0; a < 3; ++a) {
+    for (int a = 0; a < 3 && depth < MAX_SAH_DEPTH; ++a) {
       float ext = cbox.hi[a] - cbox.lo[a];
       if (!(ext > 0.0f)) continue;
       Box bb[SAH_BINS];
@@ -115,8 +119,8 @@ struct Builder {
       mid = first + count / 2;  // all centroids coincide: split by count
     }
     if (mid == first || mid == first + count) mid = first + count / 2;
-    int l = build(first, mid - first);
-    int r = build(mid, first + count - mid);
+    int l = build(first, mid - first, depth + 1);
+    int r = build(mid, first + count - mid, depth + 1);
     bin[idx].left = l;
     bin[idx].right = r;
     return idx;

@@ -87,6 +87,12 @@ struct Replica {
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_up[16] = {}, ev_k[16] = {};  // per row chunk: upload done, kernel done
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // fan-out of one frame over the replicas (no timing)
+  // heavy-first block scheduling (HeavySched, rt_scene.h): what the previous launch on this replica learned
+  std::mutex heavy_mu;
+  uint32_t *heavy_mem = nullptr;  // [2 x HEAVY_CAP lists | 2 counts | done[tiles] | seen[tiles]]
+  size_t heavy_tiles = 0;
+  uint64_t heavy_sig = 0;         // frame geometry + kernel shape the lists were built for
+  uint32_t heavy_parity = 0, heavy_tag = 0;
 };
 
 struct rt_scene {
@@ -210,6 +216,7 @@ void replica_free(Replica &r) {
     if (e) cudaEventDestroy(e);
   if (r.ev_fork) cudaEventDestroy(r.ev_fork);
   if (r.ev_join) cudaEventDestroy(r.ev_join);
+  if (r.heavy_mem) cudaFree(r.heavy_mem);
   if (r.h_stream) cudaStreamDestroy(r.h_stream);
   if (r.h_up) cudaStreamDestroy(r.h_up);
   if (r.h_down) cudaStreamDestroy(r.h_down);
@@ -524,6 +531,17 @@ const int g_env_oct_refill = env_int("RT_OCT_REFILL");
 const int g_env_oct_batch = env_int("RT_OCT_BATCH");
 // RT_MULTI=0: scenes with several replicas (rt_init) still render on one device per call (A/B measurements)
 const int g_env_multi = std::getenv("RT_MULTI") ? env_int("RT_MULTI") : 1;
+// Heavy-first block scheduling (rt_scene.h: HeavySched).  RT_HEAVY_CYCLES: SM cycles above which a block counts as heavy
+// and starts first in the next launch (0 = off).  RT_HEAVY_MIN_RAYS / RT_HEAVY_MAX_RAYS: the launch sizes it is used for.
+// Measured on one box against the kernels without it (profiles/r2_heavy_ab.txt, kernel ms): one GPU's share of a 4K
+// frame over 8 / 4 GPUs, 513^3 grid 0.104 -> 0.088 / 0.138 -> 0.126, bunny 0.080 -> 0.070 / 0.129 -> 0.109; 1080p full
+// frame 0.112 -> 0.109 (grid), 0.169 -> 0.160 (default look).  A full 4K frame would lose 4-6 % (the tail it removes is
+// small there, the slot blocks and the per-block look-up are not) and frames under ~0.5 Mrays lose more (cube 512^2:
+// +20 %): both stay on the plain kernels, which are compiled without any of it.
+constexpr int HEAVY_CYCLES_DEFAULT = 35000;
+const int g_env_heavy = std::getenv("RT_HEAVY_CYCLES") ? env_int("RT_HEAVY_CYCLES") : HEAVY_CYCLES_DEFAULT;
+const long long g_env_heavy_min_rays = std::getenv("RT_HEAVY_MIN_RAYS") ? std::atoll(std::getenv("RT_HEAVY_MIN_RAYS")) : 600000ll;
+const long long g_env_heavy_max_rays = std::getenv("RT_HEAVY_MAX_RAYS") ? std::atoll(std::getenv("RT_HEAVY_MAX_RAYS")) : 3300000ll;
 
 // per-scene-type default scheduling, chosen by measurement (profiles/r1_tune.txt): the octree
 // descent has the most uneven per-warp cost and gains from persistent warps pulling tiles; the grid marcher, the BVH
@@ -551,8 +569,48 @@ bool staged_kernel_available(const FrameDev &fd, const void *counters) {
   return (sched_now == RT_SCHED_AUTO || sched_now == RT_SCHED_TILES) && !counters && fd.W % 8u == 0u;
 }
 
+// Points a launch at the replica's heavy-first state (rt_scene.h: HeavySched).  Order only; see the notes there.
+int prepare_heavy(Replica &rep, const FrameDev &fd, int kernel_shape, HeavySched &h, cudaStream_t st) {
+  h = HeavySched{};
+  const long long rays = (long long)fd.W * fd.rows_here;
+  if (g_env_heavy <= 0 || rays > g_env_heavy_max_rays || rays < g_env_heavy_min_rays) return RT_OK;
+  std::lock_guard<std::mutex> lock(rep.heavy_mu);
+  const size_t tiles = (size_t)((fd.W + 7u) / 8u) * ((fd.rows_here + 3u) / 4u);  // the finest tile shape bounds them all
+  if (tiles > rep.heavy_tiles || !rep.heavy_mem) {
+    if (rep.heavy_mem) RT_CUDA(cudaFree(rep.heavy_mem));  // (synchronises with launches still using it)
+    rep.heavy_mem = nullptr;
+    rep.heavy_tiles = 0;
+    const size_t words = 2 * (size_t)HEAVY_CAP + 2 + 2 * tiles;
+    RT_CUDA(cudaMalloc(&rep.heavy_mem, words * 4));
+    RT_CUDA(cudaMemset(rep.heavy_mem, 0, words * 4));
+    rep.heavy_tiles = tiles;
+    rep.heavy_sig = 0;
+  }
+  uint32_t *lists = rep.heavy_mem, *counts = lists + 2 * HEAVY_CAP, *done = counts + 2, *seen = done + rep.heavy_tiles;
+  const uint64_t sig = ((uint64_t)fd.W << 40) ^ ((uint64_t)fd.rows_here << 20) ^ ((uint64_t)fd.band_count << 12) ^
+                       ((uint64_t)fd.band_index << 4) ^ ((uint64_t)fd.band_rows << 52) ^ (uint64_t)kernel_shape;
+  const uint32_t prev = rep.heavy_parity, next = prev ^ 1u;
+  if (sig != rep.heavy_sig) {  // another frame geometry: tile ids of the old list mean nothing
+    RT_CUDA(cudaMemsetAsync(counts + prev, 0, 4, st));
+    rep.heavy_sig = sig;
+  }
+  RT_CUDA(cudaMemsetAsync(counts + next, 0, 4, st));
+  h.prev = lists + prev * HEAVY_CAP;
+  h.prev_count = counts + prev;
+  h.next = lists + next * HEAVY_CAP;
+  h.next_count = counts + next;
+  h.done = done;
+  h.seen = seen;
+  if (++rep.heavy_tag == 0u) ++rep.heavy_tag;  // never 0 (the arrays start zeroed)
+  h.tag = rep.heavy_tag;
+  h.cycles = (uint32_t)g_env_heavy;
+  rep.heavy_parity = next;
+  return RT_OK;
+}
+
 int render_on_stream(const rt_scene *scene, Replica &rep, const FrameDev &fd, uint32_t *color, const float *t_in,
-                     float *t_out, uint32_t *prim, rt_counters *counters_dev, cudaStream_t st, int store = STORE_AUTO) {
+                     float *t_out, uint32_t *prim, rt_counters *counters_dev, cudaStream_t st, int store = STORE_AUTO,
+                     bool allow_heavy = true) {
   RenderArgs a;
   a.scene = rep.dev;
   a.frame = fd;
@@ -581,6 +639,11 @@ int render_on_stream(const rt_scene *scene, Replica &rep, const FrameDev &fd, ui
   // RT_SCHED_COMPACT thresholds: best point of the sweep in profiles/r1_tune.txt (RT_OCT_REFILL / RT_OCT_BATCH override)
   a.oct_refill_min = g_env_oct_refill > 0 ? g_env_oct_refill : 32;
   a.oct_leaf_batch = g_env_oct_batch > 0 ? g_env_oct_batch : 6;
+  a.heavy = HeavySched{};
+  if (allow_heavy && sched == RT_SCHED_TILES && !counters_dev) {
+    const int rc = prepare_heavy(rep, fd, (a.stage_stores ? 1 : 0) | (a.tile_block << 2) | (scene->kind << 12), a.heavy, st);
+    if (rc) return rc;
+  }
   cudaError_t e = (g_math.load() == RT_MATH_FAST) ? fast::launch_render(a, sched, rep.sm_count, st)
                                                   : exact::launch_render(a, sched, rep.sm_count, st);
   if (e != cudaSuccess) return cuda_fail(e, "render launch");
@@ -1015,7 +1078,7 @@ int rt_render_host(const rt_scene *scene_c, const rt_frame *frame, uint32_t *col
       RT_CUDA(cudaStreamWaitEvent(st, r.ev_up[k], 0));
     }
     rc = render_on_stream(s, r, fk, r.h_color, r.h_t, r.h_t, prim ? r.h_prim : nullptr, counters ? r.h_cnt : nullptr, st,
-                          STORE_PLAIN);
+                          STORE_PLAIN, n_chunks == 1);
     if (rc) return rc;
     RT_CUDA(cudaEventRecord(r.ev_k[k], st));
     RT_CUDA(cudaStreamWaitEvent(r.h_down, r.ev_k[k], 0));

@@ -103,25 +103,81 @@ __device__ __forceinline__ uint32_t centre_out(uint32_t i, uint32_t n) {
   return (i & 1u) ? mid - 1u - k : mid + k;
 }
 
+// ---- heavy-first block scheduling (HeavySched, rt_scene.h) ----------------------------------------------------
+// HEAVY instantiations only (the others compile to exactly the plain kernels: three more live registers were enough to
+// cost the 48-register grid marcher 16 %, so the state a block needs at its end lives in shared memory instead).
+// The grid is (tilesX, extra_rows + tilesY): the leading extra_rows rows of blocks are slots for the tiles that ran long
+// in the previous launch, the rest is the regular grid.  -> the tile position (bx, byi: default-order row, before
+// centre_out) this block renders, or false when it has nothing to do.  The answer is the same for every thread of the
+// block (one thread looks, the block votes), so a tile is never half rendered.
+struct HeavyBlock {
+  uint32_t tile;     // this block's tile id
+  uint32_t t0[8];    // per warp: clock() when it started
+};
+__device__ __forceinline__ bool heavy_pick(const HeavySched &h, HeavyBlock &hb, uint32_t tilesX, uint32_t nTiles,
+                                           uint32_t &bx, uint32_t &byi) {
+  if ((threadIdx.x & 31u) == 0u) hb.t0[threadIdx.x >> 5] = (uint32_t)clock();
+  if (blockIdx.y < h.extra_rows) {
+    const uint32_t slot = blockIdx.y * tilesX + blockIdx.x;
+    if (threadIdx.x == 0) hb.tile = slot < min(__ldcg(h.prev_count), HEAVY_CAP) ? __ldcg(h.prev + slot) : 0xFFFFFFFFu;
+    __syncthreads();
+    const uint32_t tile = hb.tile;
+    if (tile >= nTiles) return false;  // empty slot, or a list built for another frame geometry
+    byi = tile / tilesX;
+    bx = tile - byi * tilesX;
+    if (threadIdx.x == 0) __stcg(h.done + tile, h.tag);
+    return true;
+  }
+  byi = blockIdx.y - h.extra_rows;
+  bx = blockIdx.x;
+  const uint32_t tile = byi * tilesX + bx;
+  int taken = 0;
+  if (threadIdx.x == 0) {
+    hb.tile = tile;
+    taken = __ldcg(h.done + tile) == h.tag;
+  }
+  return !__syncthreads_or(taken);
+}
+// called by every warp when its pixels are done
+__device__ __forceinline__ void heavy_report(const HeavySched &h, const HeavyBlock &hb) {
+  if ((threadIdx.x & 31u) == 0u && (uint32_t)clock() - hb.t0[threadIdx.x >> 5] > h.cycles) {
+    const uint32_t tile = hb.tile;
+    if (atomicExch(h.seen + tile, h.tag) != h.tag) {
+      const uint32_t k = atomicAdd(h.next_count, 1u);
+      if (k < HEAVY_CAP) h.next[k] = tile;
+    }
+  }
+}
+
 // ---- RT_SCHED_TILES: one thread per pixel -------------------------------------------------------------------
 // A block is WX x WY warp tiles.  An SM releases a block's registers and warp slots only when its LAST warp retires,
 // so with long-tailed per-ray costs (one grazing ray marching 100+ steps) big blocks strand resident-warp slots
 // behind their slowest warp; the block shape per scene kind is chosen by measurement.
-template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY>
+template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY, bool HEAVY>
 // (BVH only: capping the traversal at 64 registers buys 8 resident blocks and measured 5 % on both meshes; the same cap
 // slows the grid and octree kernels, profiles/r1_tune.txt)
 __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * WX * WY) : 0) render_tiles_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
+  __shared__ HeavyBlock hb;
+  uint32_t bx = blockIdx.x, byi = blockIdx.y, tilesY = gridDim.y;
+  if (HEAVY) {
+    tilesY = gridDim.y - a.heavy.extra_rows;
+    if (!heavy_pick(a.heavy, hb, gridDim.x, gridDim.x * tilesY, bx, byi)) return;
+  }
   if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t x = (blockIdx.x * WX + warp % WX) * TILE_W + (lane & 7u);
-  const uint32_t v = (centre_out(blockIdx.y, gridDim.y) * WY + warp / WX) * TILE_H + (lane >> 3);
+  const uint32_t x = (bx * WX + warp % WX) * TILE_W + (lane & 7u);
+  const uint32_t v = (centre_out(byi, tilesY) * WY + warp / WX) * TILE_H + (lane >> 3);
   Counters cnt = {};
   if (x < a.frame.W && v < a.frame.rows_here) {
     const uint32_t row = band_row(a.frame, v);
     if (row < a.frame.H) shade_pixel<KIND, COUNT, SECONDARY>(a, smemTris, x, row, cnt);
   }
   if (COUNT) flush_counters(cnt, a.counters);
+  if (HEAVY) {
+    __syncwarp();
+    heavy_report(a.heavy, hb);
+  }
 }
 
 // ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (peer or pinned-host framebuffer) --------
@@ -136,17 +192,23 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
 //   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous colour and depth are
 //                  first fetched into the same shared-memory rows by bulk loads completing on an mbarrier; a pixel is
 //                  replaced only by a nearer hit, and the whole tile goes back.
-template <int KIND, bool INOUT, bool SECONDARY>
+template <int KIND, bool INOUT, bool SECONDARY, bool HEAVY>
 __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
   __shared__ __align__(128) uint32_t sColor[4][32];
   __shared__ __align__(128) float sDepth[4][32];
   __shared__ __align__(128) uint32_t sPrim[4][32];
   __shared__ __align__(8) unsigned long long mbar;
-  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const FrameDev &f = a.frame;
+  __shared__ HeavyBlock hb;
+  uint32_t bxi = blockIdx.x, byi = blockIdx.y, tilesY = gridDim.y;
+  if (HEAVY) {
+    tilesY = gridDim.y - a.heavy.extra_rows;
+    if (!heavy_pick(a.heavy, hb, gridDim.x, gridDim.x * tilesY, bxi, byi)) return;
+  }
+  if (KIND == KIND_BRUTE) stage_triangles(a.scene.mesh, smemTris);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t x0 = blockIdx.x * 32u, v0 = centre_out(blockIdx.y, gridDim.y) * 4u;
+  const uint32_t x0 = bxi * 32u, v0 = centre_out(byi, tilesY) * 4u;
   const uint32_t lx = warp * TILE_W + (lane & 7u), ly = lane >> 3;
   const uint32_t x = x0 + lx, v = v0 + ly;
   const uint32_t rowBytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
@@ -245,6 +307,7 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
   }
+  if (HEAVY) heavy_report(a.heavy, hb);
 }
 
 // ---- RT_SCHED_PERSISTENT: persistent warps, dynamic tile fetch ------------------------------------------------
@@ -417,12 +480,31 @@ static inline int kind_of(const SceneDev &s) {
   return s.mesh.brute ? KIND_BRUTE : KIND_BVH;
 }
 
+template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY, bool HEAVY>
+static cudaError_t launch_tiles_shape_h(const RenderArgs &a, size_t smem, cudaStream_t st) {
+  auto kern = render_tiles_kernel<KIND, COUNT, SECONDARY, WX, WY, HEAVY>;
+  if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const uint32_t tx = (a.frame.W + TILE_W * WX - 1u) / (TILE_W * WX), ty = (a.frame.rows_here + TILE_H * WY - 1u) / (TILE_H * WY);
+  RenderArgs b = a;
+  b.heavy.extra_rows = HEAVY ? (HEAVY_CAP + tx - 1u) / tx : 0u;
+  kern<<<dim3(tx, ty + b.heavy.extra_rows), 32 * WX * WY, smem, st>>>(b);
+  return cudaGetLastError();
+}
+// heavy-first scheduling exists for the default block shape of the kernels that are timed (no counters)
 template <int KIND, bool COUNT, bool SECONDARY, int WX, int WY>
 static cudaError_t launch_tiles_shape(const RenderArgs &a, size_t smem, cudaStream_t st) {
-  auto kern = render_tiles_kernel<KIND, COUNT, SECONDARY, WX, WY>;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  dim3 grid((a.frame.W + TILE_W * WX - 1u) / (TILE_W * WX), (a.frame.rows_here + TILE_H * WY - 1u) / (TILE_H * WY));
-  kern<<<grid, 32 * WX * WY, smem, st>>>(a);
+  if (!COUNT && WX == 2 && WY == 2 && a.heavy.cycles) return launch_tiles_shape_h<KIND, false, SECONDARY, 2, 2, true>(a, smem, st);
+  return launch_tiles_shape_h<KIND, COUNT, SECONDARY, WX, WY, false>(a, smem, st);
+}
+
+template <int KIND, bool INOUT, bool SECONDARY, bool HEAVY>
+static cudaError_t launch_staged_h(const RenderArgs &a, size_t smem, cudaStream_t st) {
+  auto kern = render_tiles_staged_kernel<KIND, INOUT, SECONDARY, HEAVY>;
+  if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const uint32_t tx = (a.frame.W + 31u) / 32u, ty = (a.frame.rows_here + 3u) / 4u;
+  RenderArgs b = a;
+  b.heavy.extra_rows = HEAVY ? (HEAVY_CAP + tx - 1u) / tx : 0u;
+  kern<<<dim3(tx, ty + b.heavy.extra_rows), 128, smem, st>>>(b);
   return cudaGetLastError();
 }
 
@@ -458,17 +540,11 @@ static cudaError_t launch_render_t(const RenderArgs &a, int sched, int sm_count,
     const int tb = a.tile_block;
     if (KIND == KIND_BRUTE && !(!COUNT && a.stage_stores)) return launch_tiles_shape<KIND, COUNT, SECONDARY, 4, 2>(a, smem, st);
     if (!COUNT && a.stage_stores) {
-      dim3 grid((a.frame.W + 31u) / 32u, (a.frame.rows_here + 3u) / 4u);
-      if (a.stage_stores == 2) {
-        auto kern = render_tiles_staged_kernel<KIND, true, SECONDARY>;
-        if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        kern<<<grid, 128, smem, st>>>(a);
-      } else {
-        auto kern = render_tiles_staged_kernel<KIND, false, SECONDARY>;
-        if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        kern<<<grid, 128, smem, st>>>(a);
-      }
-      return cudaGetLastError();
+      if (a.stage_stores == 2)
+        return a.heavy.cycles ? launch_staged_h<KIND, true, SECONDARY, true>(a, smem, st)
+                              : launch_staged_h<KIND, true, SECONDARY, false>(a, smem, st);
+      return a.heavy.cycles ? launch_staged_h<KIND, false, SECONDARY, true>(a, smem, st)
+                            : launch_staged_h<KIND, false, SECONDARY, false>(a, smem, st);
     }
     if (!COUNT && !SECONDARY) {
       if (tb == 32) return launch_tiles_shape<KIND, false, false, 1, 1>(a, smem, st);

@@ -109,9 +109,30 @@ struct FrameDev {
   int32_t clear;
 };
 
+// Heavy-first block scheduling (tiles kernels).  A frame cannot finish before its longest ray does: one grazing ray
+// marching 150 dependent, cache-missing steps takes 20-60 us however many SMs are idle, and launched mid-frame it IS the
+// tail.  That fixed cost is what a share of a frame on one of 8 GPUs, or a 1080p frame, mostly consists of (4K 513^3
+// grid: 0.366 ms on one GPU, 0.103 ms for an eighth of it).  Successive frames of a viewer are nearly the same picture,
+// so every launch records which blocks ran long and the next launch of the same scene / frame geometry starts those
+// first: the grid carries extra leading rows of blocks that pick their tile from the previous launch's list; the
+// regular blocks skip tiles already taken that way.  Order only: every pixel is still rendered by exactly the same code
+// (a stale or racing list can cost redundant work, never a missing or half-rendered tile).
+constexpr uint32_t HEAVY_CAP = 2048;
+struct HeavySched {
+  const uint32_t *prev;        // tile ids (default-order block index) that ran long in the previous launch
+  const uint32_t *prev_count;  // how many of them (device memory; <= HEAVY_CAP are used)
+  uint32_t *next, *next_count; // this launch's own list
+  uint32_t *done;              // [tile] == tag: this launch took the tile from `prev`
+  uint32_t *seen;              // [tile] == tag: this launch has already reported the tile
+  uint32_t tag;                // unique per launch
+  uint32_t cycles;             // a block is heavy when one of its warps ran longer than this; 0 = scheduling off
+  uint32_t extra_rows;         // leading grid rows that are heavy slots (set by the launcher)
+};
+
 struct RenderArgs {
   SceneDev scene;
   FrameDev frame;
+  HeavySched heavy;
   uint32_t *color;
   const float *t_in;
   float *t_out;

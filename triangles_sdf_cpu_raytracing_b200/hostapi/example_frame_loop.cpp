@@ -2,6 +2,8 @@
 //   example_frame_loop <scene.grid|.octree|.obj> <W> <H> <normal|lambert|color> <plane 0|1> <out.raw> [orbit steps [pinned]]
 // "pinned": FrameBuffer::pin() + Renderer::frameIsCleared, the page-locked framebuffer the kernel stores straight into.
 // out.raw = W*H uint32 colour followed by W*H float depth (the FrameBuffer contents after draw).
+// RT_DEVICES=0,1,2,... in the environment lists the GPUs (rt_init): the same single renderer.draw call then renders
+// every frame on all of them.
 // An output name ending in .ppm writes the colour buffer as a binary PPM instead (the headless stand-in for the
 // viewer's SDL blit, main.cpp:238-249); with orbit steps one file per frame: name_000.ppm, name_001.ppm, ...
 #include <cstdio>
@@ -10,6 +12,7 @@
 #include <fstream>
 #include <memory>
 #include <string>
+#include <vector>
 
 #include "scenes.hpp"
 
@@ -50,6 +53,15 @@ int main(int argc, char **argv) {
     const std::string outName = argv[6];
     const bool ppm = ends_with(outName, ".ppm");
 
+    if (const char *list = std::getenv("RT_DEVICES")) {  // before any scene is created
+      std::vector<int> devs;
+      for (const char *p = list; *p;) {
+        devs.push_back(std::atoi(p));
+        while (*p && *p != ',') ++p;
+        if (*p == ',') ++p;
+      }
+      if (rt_init(devs.data(), static_cast<int>(devs.size())) != RT_OK) throw std::runtime_error(rt_last_error());
+    }
     std::shared_ptr<IScene> pScene;  // main.cpp:167-191
     float planeY = -1.0f;
     if (ends_with(path, ".grid")) {

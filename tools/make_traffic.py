@@ -1,12 +1,15 @@
 #!/usr/bin/env python
-"""profiles/r1_*_full.txt (ncu --set full summaries) -> profiles/traffic.json: per workload the DRAM bytes and the
+"""profiles/r<round>_*_full.txt (ncu --set full summaries; a later round's capture of a workload replaces the earlier
+one) -> profiles/traffic.json: per workload the DRAM bytes and the
 warp instructions of ONE launch of the render kernel, which bench.py folds into its roofline object."""
 import glob, json, os, re
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 UNIT = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 out = {}
-for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r1_*_full.txt"))):
+for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9]_*_full.txt"))):
     name = os.path.basename(f)[3:-9]
+    if os.path.basename(f) in ("r1_cube_512_full.txt", "r1_octree6_4k_full.txt"):  # kernels changed since (octree: round 2)
+        continue  # round 1 ran cube.obj through the small-mesh kernel; RT_MESH_AUTO now builds a tree for 12 triangles
     txt = open(f).read().split("## launch 1")[0]
     def metric(m):
         r = re.search(rf"^{re.escape(m)}\s+([0-9.]+)\s*(\S*)", txt, re.M)

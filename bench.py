@@ -73,7 +73,7 @@ def hbm_peak():
 def measured_roofs():
     """FP32 (with / without FMA), issue rate, cached-gather rates and dependent-load latencies measured on THIS box by
     tools/peaks (hand-written micro-benchmarks), cached per box; the committed capture of an earlier box otherwise."""
-    cache = "/tmp/rt_b200_peaks.json"
+    cache = os.environ.get("RT_PEAKS_CACHE", "/tmp/rt_b200_peaks.json")
     if os.path.exists(cache):
         return json.load(open(cache)), "tools/peaks on this box"
     exe = os.path.join(ROOT, "tools", "peaks")

@@ -447,3 +447,82 @@ def test_brute_force_path_box_cull_and_depth_bound():
                         drew_nothing += int(np.isinf(got["t"]).all())
     assert drew_nothing == 4
     s.destroy()
+
+
+def _octree_with_shared_leaves():
+    """Root (children 1..8); children 1 and 6 are inner nodes that SHARE one block of 8 leaves (9..16): a file with
+    de-duplicated leaves, which the reference's loader and intersectNode accept (octree_raytracing.cpp:8-16,166-202)."""
+    n = 17
+    rec = np.zeros((n, 9), np.uint32)
+    val = rec[:, :8].view(np.float32)
+    rec[0, 8] = 1
+    val[1:9] = 1000.0            # empty-outside leaves ...
+    rec[1, 8] = 9                # ... except two inner nodes pointing at the same block
+    rec[6, 8] = 9
+    val[1] = 0.0
+    val[6] = 0.0
+    rng = np.random.default_rng(11)
+    val[9:17] = rng.uniform(-0.2, 0.3, (8, 8)).astype(np.float32)   # surface leaves
+    val[12] = 1000.0             # one culled leaf inside the shared block
+    return rec.view(np.uint8).reshape(n, 36)
+
+
+def test_octree_with_shared_leaves_loads_and_matches_the_oracle():
+    from oracle import port_oracle as P
+    nodes = _octree_with_shared_leaves()
+    s = rt.SDFOctree(nodes)
+    ps = P.Scene.octree(nodes)
+    c = G.case("sdf_6|default|160x90")
+    for cam in ("sdf_6|default|160x90", "sdf_6|orbit23tilt|96x64"):
+        c = G.case(cam)
+        want_c, want_t, _, want_cnt = ps.render(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"], want_counters=True)
+        r = s.render(_frame(c), want_counters=True)
+        assert util.same_bits(r["t"], want_t) and np.array_equal(r["color"], want_c), cam
+        assert r["counters"]["oct_inner"] == want_cnt["octInner"] and r["counters"]["oct_leaf"] == want_cnt["octLeaf"]
+        r2 = s.render(_frame(c))  # the plain flavour drops culled children when it builds its lists
+        assert util.same_bits(r2["t"], want_t) and np.array_equal(r2["color"], want_c), cam
+    assert np.isfinite(want_t).any()
+    # an inner node referenced twice is how a cycle would look: rejected
+    bad = nodes.copy().view(np.uint32).reshape(-1, 9)
+    bad[9, 8] = 1  # leaf 9 becomes an inner node pointing back at the root's children
+    with pytest.raises(rt.RtError):
+        rt.SDFOctree(bad.view(np.uint8).reshape(-1, 36))
+
+
+def test_pinned_buffers_the_bulk_copies_cannot_address_fall_back_to_the_copy_pipeline():
+    """rt_render_host takes the kernel-stores-to-host route only for 16-byte aligned, fully page-locked buffers
+    (include/rt_b200.h); an offset or partly registered range silently takes the copies and still returns the frame."""
+    import ctypes as C
+    import torch
+    from triangles_sdf_cpu_raytracing_b200 import _lib as L
+    c = G.case("example_grid|default|160x90")
+    s = scene("example_grid")
+    W, H = c["W"], c["H"]
+    f = rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True)
+    big_c = torch.zeros(W * H + 64, dtype=torch.int32).pin_memory()
+    big_t = torch.zeros(W * H + 64, dtype=torch.float32).pin_memory()
+    for off in (1, 3):  # 4- and 12-byte offsets: not 16-byte aligned
+        col, t = big_c[off:off + W * H], big_t[off:off + W * H]
+        col.fill_(0x5A5A5A5A)
+        t.fill_(0.25)
+        L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(col.data_ptr()), C.c_void_p(t.data_ptr()), None,
+                                       None, None, None))
+        assert util.same_bits(t.numpy().reshape(H, W), c["t"]) and np.array_equal(col.numpy().view(np.uint32).reshape(H, W), c["color_normal"]), off
+    # only the first half of each buffer is registered
+    def pages(dtype):
+        raw = np.empty(H * W * 4 + 8192, np.uint8)
+        o = (-raw.ctypes.data) % 4096
+        return raw[o:o + H * W * 4].view(dtype).reshape(H, W)
+    col, t = pages(np.uint32), pages(np.float32)
+    half = (H * W * 4 // 2) // 4096 * 4096
+    L.check(L.lib().rt_pinned_register(C.c_void_p(col.ctypes.data), half))
+    L.check(L.lib().rt_pinned_register(C.c_void_p(t.ctypes.data), half))
+    try:
+        col[...] = 7
+        t[...] = 0.5
+        L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(col.ctypes.data), C.c_void_p(t.ctypes.data), None,
+                                       None, None, None))
+    finally:
+        L.check(L.lib().rt_pinned_unregister(C.c_void_p(col.ctypes.data)))
+        L.check(L.lib().rt_pinned_unregister(C.c_void_p(t.ctypes.data)))
+    assert util.same_bits(t, c["t"]) and np.array_equal(col, c["color_normal"])

@@ -5,7 +5,7 @@ set -u
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-tools/peaks > gpurun_out/r2_peaks.json 2> gpurun_out/r2_peaks.err; cp gpurun_out/r2_peaks.json /tmp/rt_b200_peaks.json
+tools/peaks > gpurun_out/r2_peaks.json 2> gpurun_out/r2_peaks.err; cp gpurun_out/r2_peaks.json ${RT_PEAKS_CACHE:-/tmp/rt_b200_peaks.json}
 b() { name=$1; shift; python bench.py "$@" > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; }
 b grid513_4k --steps 50 --warmup 5
 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err

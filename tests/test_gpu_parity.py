@@ -508,7 +508,9 @@ def test_pinned_buffers_the_bulk_copies_cannot_address_fall_back_to_the_copy_pip
         L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(col.data_ptr()), C.c_void_p(t.data_ptr()), None,
                                        None, None, None))
         assert util.same_bits(t.numpy().reshape(H, W), c["t"]) and np.array_equal(col.numpy().view(np.uint32).reshape(H, W), c["color_normal"]), off
-    # only the first half of each buffer is registered
+    # Only the first half of each buffer is registered.  The kernel must not be pointed at it (an illegal address inside a
+    # kernel is a sticky fault that kills the context); the copy pipeline either copes or the runtime refuses the copy
+    # with an ordinary error (cudaMemcpyAsync rejects a range that is half pinned, half pageable), and the library goes on.
     def pages(dtype):
         raw = np.empty(H * W * 4 + 8192, np.uint8)
         o = (-raw.ctypes.data) % 4096
@@ -520,9 +522,14 @@ def test_pinned_buffers_the_bulk_copies_cannot_address_fall_back_to_the_copy_pip
     try:
         col[...] = 7
         t[...] = 0.5
-        L.check(L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(col.ctypes.data), C.c_void_p(t.ctypes.data), None,
-                                       None, None, None))
+        rc = L.lib().rt_render_host(s.handle, C.byref(f), C.c_void_p(col.ctypes.data), C.c_void_p(t.ctypes.data), None,
+                                    None, None, None)
     finally:
         L.check(L.lib().rt_pinned_unregister(C.c_void_p(col.ctypes.data)))
         L.check(L.lib().rt_pinned_unregister(C.c_void_p(t.ctypes.data)))
-    assert util.same_bits(t, c["t"]) and np.array_equal(col, c["color_normal"])
+    if rc == 0:
+        assert util.same_bits(t, c["t"]) and np.array_equal(col, c["color_normal"])
+    else:
+        assert rc == -2 and b"cudaMemcpy" in L.lib().rt_last_error()
+    r = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H))  # the context is alive and well
+    assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])

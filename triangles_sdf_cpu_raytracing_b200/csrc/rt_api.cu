@@ -43,6 +43,7 @@ int fail(int code, const std::string &msg) {
 }
 int cuda_fail(cudaError_t e, const char *what) {
   g_err = std::string(what) + ": " + cudaGetErrorString(e);
+  cudaGetLastError();  // a non-sticky error must not be reported again by the next launch's cudaGetLastError()
   return RT_ERR_CUDA;
 }
 #define RT_CUDA(call)                                  \

@@ -171,7 +171,9 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
   Counters cnt = {};
   if (x < a.frame.W && v < a.frame.rows_here) {
     const uint32_t row = band_row(a.frame, v);
-    if (row < a.frame.H) shade_pixel<KIND, COUNT, SECONDARY>(a, smemTris, x, row, cnt);
+    // (small launches are decided by their longest march: the HEAVY flavour of the linear grid prefetches along it)
+    constexpr int K = (HEAVY && KIND == KIND_GRID) ? KIND_GRID_PF : KIND;
+    if (row < a.frame.H) shade_pixel<K, COUNT, SECONDARY>(a, smemTris, x, row, cnt);
   }
   if (COUNT) flush_counters(cnt, a.counters);
   if (HEAVY) {
@@ -270,7 +272,8 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
       C4 col;
       float tNew = __int_as_float(0x7f800000);
       uint32_t prim;
-      if (intersection_color<KIND, false, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
+      constexpr int K = (HEAVY && KIND == KIND_GRID) ? KIND_GRID_PF : KIND;
+      if (intersection_color<K, false, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
           !isinf(tNew)) {
         sColor[ly][lx] = color_pack_rgba(col);
         sDepth[ly][lx] = tNew;

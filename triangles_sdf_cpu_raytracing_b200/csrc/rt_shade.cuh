@@ -4,6 +4,7 @@
 // also compiles as plain C++ (tests/host_emul/, where the parity tests run it on the CPU against the oracle).
 
 constexpr int KIND_GRID = 0, KIND_OCTREE = 1, KIND_BVH = 2, KIND_BRUTE = 3, KIND_GRID_BRICKS = 4;
+constexpr int KIND_GRID_PF = 5;  // the linear grid with prefetch along long marches (small launches, rt_device.cuh)
 
 // IScene::intersect of the model, and of SceneUnion(model, plane) (raytracing.hpp:83-97)
 template <int KIND, bool COUNT>
@@ -11,6 +12,7 @@ __device__ __forceinline__ Hit model_intersect(const SceneDev &s, const float4 *
                                                float tFar, Counters &cnt) {
   if (COUNT) cnt.rays++;
   if (KIND == KIND_GRID) return grid_intersect<false, COUNT>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_GRID_PF) return grid_intersect<false, COUNT, true>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_GRID_BRICKS) return grid_intersect<true, COUNT>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_OCTREE) return oct_intersect<COUNT>(s.oct, o, d, tNear, tFar, cnt);
   if (KIND == KIND_BVH) return bvh_intersect<COUNT>(s.mesh, o, d, tNear, tFar, cnt);

@@ -191,9 +191,10 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
 // the bulk engine has READ its shared memory (wait_group.read), not until the writes have landed on the far side of
 // the link: the grid's completion covers that.  W % 8 == 0.
 //   INOUT = false: fused clear, every pixel of the tile is produced here.
-//   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous colour and depth are
-//                  first fetched into the same shared-memory rows by bulk loads completing on an mbarrier; a pixel is
-//                  replaced only by a nearer hit, and the whole tile goes back.
+//   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous DEPTH is first fetched
+//                  into shared memory by bulk loads completing on an mbarrier (it bounds every ray of the tile); a tile
+//                  without any nearer hit is then left alone, a fully hit one is stored whole, and only a partly hit
+//                  one fetches its previous colour (and prim ids) so that the rows that go back are complete.
 template <int KIND, bool INOUT, bool SECONDARY, bool HEAVY>
 __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
@@ -215,42 +216,22 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
   const uint32_t x = x0 + lx, v = v0 + ly;
   const uint32_t rowBytes = min(32u, f.W - x0) * 4u;  // W % 8 == 0: a multiple of 32 bytes, 16-byte aligned
   const bool wantPrim = a.prim != nullptr;
-  if (INOUT) {
-    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
-    if (threadIdx.x == 0) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t rows = 0;
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
+  // thread 0: bulk-load the tile's rows of one framebuffer plane into shared memory, completing on the mbarrier
+  auto load_rows = [&](const void *plane, uint32_t sdst) {
 #pragma unroll
-      for (uint32_t r = 0; r < 4u; ++r)
-        if (v0 + r < f.rows_here && band_row(f, v0 + r) < f.H) ++rows;
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
-                   "r"(rows * (wantPrim ? 3u : 2u) * rowBytes)
+    for (uint32_t r = 0; r < 4u; ++r) {
+      if (!(v0 + r < f.rows_here)) continue;
+      const uint32_t row = band_row(f, v0 + r);
+      if (!(row < f.H)) continue;
+      const size_t px = (size_t)row * f.W + x0;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       sdst + r * 128u),
+                   "l"(static_cast<const uint32_t *>(plane) + px), "r"(rowBytes), "r"(bar)
                    : "memory");
-#pragma unroll
-      for (uint32_t r = 0; r < 4u; ++r) {
-        if (!(v0 + r < f.rows_here)) continue;
-        const uint32_t row = band_row(f, v0 + r);
-        if (!(row < f.H)) continue;
-        const size_t px = (size_t)row * f.W + x0;
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         (uint32_t)__cvta_generic_to_shared(&sColor[r][0])),
-                     "l"(a.color + px), "r"(rowBytes), "r"(bar)
-                     : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         (uint32_t)__cvta_generic_to_shared(&sDepth[r][0])),
-                     "l"(a.t_in + px), "r"(rowBytes), "r"(bar)
-                     : "memory");
-        if (wantPrim)
-          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                           (uint32_t)__cvta_generic_to_shared(&sPrim[r][0])),
-                       "l"(a.prim + px), "r"(rowBytes), "r"(bar)
-                       : "memory");
-      }
     }
+  };
+  auto wait_phase = [&](uint32_t parity) {
     uint32_t done = 0;
     while (!done) {
       asm volatile(
@@ -258,14 +239,37 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
           "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
           "selp.u32 %0, 1, 0, p;\n\t}"
           : "=r"(done)
-          : "r"(bar), "r"(0)
+          : "r"(bar), "r"(parity)
           : "memory");
     }
+  };
+  uint32_t rowsHere = 0;
+#pragma unroll
+  for (uint32_t r = 0; r < 4u; ++r)
+    if (v0 + r < f.rows_here && band_row(f, v0 + r) < f.H) ++rowsHere;
+  if (INOUT) {
+    // the previous DEPTH of the tile is all a ray needs (tPrev bounds it); colour and prim ids are only fetched later,
+    // and only if the tile ends up partly hit (a tile with no nearer hit is not touched at all, a fully hit one is
+    // overwritten whole)
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowsHere * rowBytes) : "memory");
+      load_rows(a.t_in, (uint32_t)__cvta_generic_to_shared(&sDepth[0][0]));
+    }
+    wait_phase(0);
   }
   Counters cnt = {};
+  bool inFrame = false, hit = false;
+  uint32_t myColor = 0u, myPrim = RT_PRIM_MISS;
+  float myT = __int_as_float(0x7f800000);
   if (x < f.W && v < f.rows_here) {
     const uint32_t row = band_row(f, v);
     if (row < f.H) {
+      inFrame = true;
       const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
       const V3 d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
       const float tPrev = INOUT ? sDepth[ly][lx] : __int_as_float(0x7f800000);
@@ -275,15 +279,38 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
       constexpr int K = (HEAVY && KIND == KIND_GRID) ? KIND_GRID_PF : KIND;
       if (intersection_color<K, false, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
           !isinf(tNew)) {
-        sColor[ly][lx] = color_pack_rgba(col);
-        sDepth[ly][lx] = tNew;
-        if (wantPrim) sPrim[ly][lx] = prim;
-      } else if (!INOUT) {  // fused FrameBuffer::clear (raytracing.hpp:16-19)
-        sColor[ly][lx] = 0u;
-        sDepth[ly][lx] = __int_as_float(0x7f800000);
-        if (wantPrim) sPrim[ly][lx] = RT_PRIM_MISS;
+        hit = true;
+        myColor = color_pack_rgba(col);
+        myT = tNew;
+        myPrim = prim;
       }
     }
+  }
+  if (INOUT) {
+    const int nHit = __syncthreads_count(hit), nIn = __syncthreads_count(inFrame);
+    if (nHit == 0) {  // nothing nearer anywhere in the tile: the framebuffer keeps what it holds
+      if (HEAVY) heavy_report(a.heavy, hb);
+      return;
+    }
+    if (nHit < nIn) {  // partly hit: the pixels that keep their value need it in the rows that go back
+      if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                     "r"(rowsHere * (wantPrim ? 2u : 1u) * rowBytes)
+                     : "memory");
+        load_rows(a.color, (uint32_t)__cvta_generic_to_shared(&sColor[0][0]));
+        if (wantPrim) load_rows(a.prim, (uint32_t)__cvta_generic_to_shared(&sPrim[0][0]));
+      }
+      wait_phase(1);
+    }
+    if (hit) {
+      sColor[ly][lx] = myColor;
+      sDepth[ly][lx] = myT;
+      if (wantPrim) sPrim[ly][lx] = myPrim;
+    }
+  } else if (inFrame) {  // fused FrameBuffer::clear (raytracing.hpp:16-19): misses carry the clear values
+    sColor[ly][lx] = myColor;
+    sDepth[ly][lx] = myT;
+    if (wantPrim) sPrim[ly][lx] = myPrim;
   }
   // every thread orders ITS generic-proxy writes of the tile before the async proxy (the bulk stores below read the
   // rows through it), then the barrier makes all of them visible to the four issuing threads

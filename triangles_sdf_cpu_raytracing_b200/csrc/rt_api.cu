@@ -856,6 +856,10 @@ int render_host_multi(rt_scene *s, const FrameDev &fd, uint32_t *color, float *t
 int render_device_multi(const rt_scene *s, Replica &owner, const FrameDev &fd, uint32_t *color, const float *t_in,
                         float *t_out, uint32_t *prim, cudaStream_t user) {
   const uint32_t n = (uint32_t)s->reps.size();
+  // The fork / join events and the replicas' streams belong to the scene: calls from several host threads enqueue their
+  // whole record / wait / launch sequence one after the other (a wait captures the event's latest record at call time,
+  // so sequences that do not interleave on the host cannot see each other's events).
+  std::lock_guard<std::mutex> lock(const_cast<rt_scene *>(s)->host_mu);
   for (auto &r : s->reps) {
     DeviceGuard g(r->device);
     if (!g.ok) return fail(RT_ERR_CUDA, "cannot select a replica's device");

@@ -364,7 +364,7 @@ def build_roofline(kind, scene_bytes, alg_bytes, alg_flops, kernel_ms, kernel_ms
         v["frac"] = v["achieved"] / v["peak"]
     # the binding roof: the largest fraction among those that are roofs at all for this access pattern (a gather figure
     # above 1 only says coherent loads beat random ones; it is reported, not chosen)
-    usable = {k: v for k, v in cands.items() if v["frac"] <= 1.2}
+    usable = {k: v for k, v in cands.items() if v["frac"] <= 1.0}
     if usable:
         bound = max(usable, key=lambda k: usable[k]["frac"])
         top = usable[bound]

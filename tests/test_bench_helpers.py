@@ -28,17 +28,17 @@ def test_roofline_object_from_committed_peaks_and_captures(tmp_path, monkeypatch
     b, f = bench.algorithmic_work("grid", cnt, rays)
     assert abs(b / rays - (32 * 6.49 + 8)) < 1e-3 and abs(f / rays - (150 + 60 * 6.49)) < 1e-3
     r = bench.build_roofline("grid", 540 << 20, b, f, 0.366, 0.36, rays, "exact", traffic["grid513_4k|exact"])
-    assert r["bound"] in ("fp32", "hbm", "l2_gather", "hbm_gather") and 0 < r["frac"] <= 1.2
+    assert r["bound"] in ("fp32", "hbm", "l2_gather", "hbm_gather") and 0 < r["frac"] <= 1.0
     assert set(r["candidates"]) == {"fp32", "gather", "hbm"}
     assert abs(r["candidates"]["fp32"]["frac"] - f / 0.366e-3 / 1e12 / peaks["fp32_nofma_tflops"]) < 1e-9
     assert 0.5 < r["issue"]["frac"] < 1.0 and r["traffic"] == traffic["grid513_4k|exact"]["dram_bytes_per_launch"]
     # the random-gather roof is beaten by coherent tiles: reported, not chosen
-    assert r["candidates"]["gather"]["frac"] > 1.2 and r["bound"] != "hbm_gather"
+    assert r["candidates"]["gather"]["frac"] > 1.0 and r["bound"] != "hbm_gather"
     # octree: 16-byte gathers over an L2-resident footprint
     cnt = dict(cnt, grid_samples=0, oct_inner=int(6.1 * rays), oct_leaf=int(5.5 * rays), oct_leaf_samples=int(2.9 * rays))
     b, f = bench.algorithmic_work("octree", cnt, rays)
     r = bench.build_roofline("octree", 22 << 20, b, f, 1.055, 1.05, rays, "exact", traffic["octree8_4k|exact"])
-    assert r["candidates"]["gather"]["peak"] == peaks["gather16_useful_gbs"]["l2_64MB"] and 0 < r["frac"] <= 1.2
+    assert r["candidates"]["gather"]["peak"] == peaks["gather16_useful_gbs"]["l2_64MB"] and 0 < r["frac"] <= 1.0
     # no capture for the workload: still a line, no traffic
     r = bench.build_roofline("mesh", 8 << 20, 1e9, 1e10, 0.3, 0.3, rays, "fast", None)
     assert r["traffic"] is None and r["candidates"]["fp32"]["peak"] == peaks["fp32_ffma_tflops"]

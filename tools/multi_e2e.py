@@ -22,6 +22,21 @@ import triangles_sdf_cpu_raytracing_b200 as rt  # noqa: E402
 from tests import util  # noqa: E402
 from triangles_sdf_cpu_raytracing_b200 import _lib as L  # noqa: E402
 
+def numa_interleave():
+    """RT_NUMA=interleave: page-locked buffers allocated from here on are spread page by page over every NUMA node
+    (set_mempolicy(MPOL_INTERLEAVE)); an experiment about what limits n GPUs storing into ONE host framebuffer."""
+    import glob
+    nodes = len(glob.glob("/sys/devices/system/node/node[0-9]*"))
+    if nodes < 2:
+        return f"{nodes} NUMA node(s): nothing to interleave"
+    libc = C.CDLL(None, use_errno=True)
+    mask = C.c_ulong((1 << nodes) - 1)
+    rc = libc.syscall(238, 3, C.byref(mask), C.c_ulong(65))  # SYS_set_mempolicy, MPOL_INTERLEAVE
+    return f"{nodes} NUMA nodes, set_mempolicy(MPOL_INTERLEAVE) rc={rc} errno={C.get_errno()}"
+
+
+if os.environ.get("RT_NUMA") == "interleave":
+    print("#", numa_interleave(), flush=True)
 scenes = sys.argv[1:] or ["grid513_4k", "grid65_1080p", "octree8_4k", "bunny_4k", "default_look_1080p"]
 avail = torch.cuda.device_count()
 reps = int(os.environ.get("REPS", "20"))

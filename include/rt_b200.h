@@ -229,6 +229,19 @@ int rt_pinned_unregister(void *host_ptr);
 int rt_memcpy_d2h(void *host, const void *dev_ptr, uint64_t bytes, void *stream);
 int rt_memcpy_h2d(void *dev_ptr, const void *host, uint64_t bytes, void *stream);
 
+/* ---- environment knobs (read once when the library is loaded; measurement and A/B runs, not needed in production) ----
+ *   RT_HOST_ZEROCOPY   0: rt_render_host always copies; 1: plain stores into pinned host memory; 2 (default): staged
+ *                      128-byte bulk transfers; 3: as 2 but the in/out contract copies
+ *   RT_STAGE_STORES    0: never stage stores into a peer framebuffer; 1: stage every launch; 2: stage for every peer
+ *                      framebuffer; unset: stage at >= 8 GPUs on >= 3 Mpixel
+ *   RT_MULTI           0: a scene replicated by rt_init still renders on one device per call
+ *   RT_MULTI_BAND_ROWS rows per interleaved band of the one-call fan-out (default 8, multiple of 4)
+ *   RT_HEAVY_CYCLES    heavy-first block order: SM cycles above which a block starts first in the next launch of the
+ *                      same scene and frame geometry (default 35000; 0 = off); RT_HEAVY_MIN_RAYS / RT_HEAVY_MAX_RAYS:
+ *                      launch sizes it applies to (default 600000 .. 3300000 rays).  Order only: output is unchanged
+ *   RT_TILE_BLOCK      threads per block of the tiles kernel (32, 64, 128, 256); RT_HOST_CHUNKS: row chunks of the
+ *                      copy pipeline; RT_OCT_REFILL / RT_OCT_BATCH: thresholds of RT_SCHED_COMPACT */
+
 #ifdef __cplusplus
 }
 #endif

@@ -819,9 +819,17 @@ int render_host_multi(rt_scene *s, const FrameDev &fd, uint32_t *color, float *t
                           STORE_PLAIN);
     if (rc) return rc;
     if (timing) RT_CUDA(cudaEventRecord(r.ev[3], st));
-    if ((rc = copy_bands(color, r.h_color, fj, cudaMemcpyDeviceToHost, st))) return rc;
-    if ((rc = copy_bands(t_inout, r.h_t, fj, cudaMemcpyDeviceToHost, st))) return rc;
-    if (prim && (rc = copy_bands(prim, r.h_prim, fj, cudaMemcpyDeviceToHost, st))) return rc;
+  }
+  // downloads in a second pass: a copy into pageable memory blocks the host until it is done, and by then every other
+  // device's kernel is already running
+  for (uint32_t j = 0; j < n && !direct; ++j) {
+    Replica &r = *s->reps[j];
+    DeviceGuard g(r.device);
+    const FrameDev fj = band_share(fd, n, j);
+    int rc;
+    if ((rc = copy_bands(color, r.h_color, fj, cudaMemcpyDeviceToHost, r.h_stream))) return rc;
+    if ((rc = copy_bands(t_inout, r.h_t, fj, cudaMemcpyDeviceToHost, r.h_stream))) return rc;
+    if (prim && (rc = copy_bands(prim, r.h_prim, fj, cudaMemcpyDeviceToHost, r.h_stream))) return rc;
   }
   if (counters) std::memset(counters, 0, sizeof *counters);
   float worst = 0.0f;

@@ -111,6 +111,7 @@ extern "C" {
 EmulScene *emul_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t sz) {
   auto *e = new EmulScene;
   e->grid.assign(values, values + (size_t)sx * sy * sz);
+  e->grid.resize(e->grid.size() + (size_t)sy * sz + sz + 1, 0.0f);  // the zero padding rt_scene_create_grid uploads
   GridDev &g = e->dev.grid;
   e->dev.kind = RT_SCENE_GRID;
   g.values = e->grid.data();

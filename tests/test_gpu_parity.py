@@ -533,3 +533,18 @@ def test_pinned_buffers_the_bulk_copies_cannot_address_fall_back_to_the_copy_pip
         assert rc == -2 and b"cudaMemcpy" in L.lib().rt_last_error()
     r = s.render(rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H))  # the context is alive and well
     assert util.same_bits(r["t"], c["t"]) and np.array_equal(r["color"], c["color_normal"])
+
+
+def test_grid_with_non_finite_samples_takes_the_literal_path():
+    """The linear-layout sampler relies on finite samples (csrc/rt_device.cuh: grid_sdf); a grid holding infinities is
+    stored bricked and sampled literally, and still equals the oracle."""
+    from oracle import port_oracle as P
+    c = G.case("example_grid|default|160x90")
+    v = G.scene_arrays("example_grid")["values"].copy()
+    far = v > 0.9
+    assert far.any()
+    v[far] = np.inf  # "far away" markers
+    want_c, want_t, _, _ = P.Scene.grid(v).render(c["rayPos"], c["viewInv"], c["projInv"], c["W"], c["H"])
+    r = rt.SDFGrid(v).render(_frame(c))
+    assert util.same_bits(r["t"], want_t) and np.array_equal(r["color"], want_c)
+    assert np.isfinite(want_t).any()

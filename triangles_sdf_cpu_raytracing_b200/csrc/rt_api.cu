@@ -283,6 +283,13 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
   g.hfx = 0.5f * g.fx; g.hfy = 0.5f * g.fy; g.hfz = 0.5f * g.fz;
   const size_t n = (size_t)sx * sy * sz;
   if (layout == RT_GRID_AUTO) layout = RT_GRID_LINEAR;  // chosen by measurement, DESIGN.md "grid layout"
+  if (layout == RT_GRID_LINEAR) {
+    // the linear-layout sampler multiplies a neighbouring sample by an exact 0 where the reference does not read it
+    // (rt_device.cuh: grid_sdf): only right for finite samples, so a grid with infinities / NaNs takes the literal path
+    bool finite = true;
+    for (size_t i = 0; i < n && finite; ++i) finite = std::isfinite(values[i]);
+    if (!finite) layout = RT_GRID_BRICKS;
+  }
   if (layout == RT_GRID_BRICKS) {
     // the layout transform runs on the device (ingest.cu): upload the linear samples once, re-tile there
     const uint32_t nby = (sy + 7) / 8, nbz = (sz + 7) / 8;
@@ -300,7 +307,20 @@ int rt_scene_create_grid(const float *values, uint32_t sx, uint32_t sy, uint32_t
     g.bricks = 1; g.stride_x = nby * nbz * 512u; g.stride_y = nbz * 512u;
   } else {
     g.bricks = 0; g.stride_x = sy * sz; g.stride_y = sz;
-    rc = upload(s, values, n, &g.values);
+    // readable zeros one slab + one row + one sample past the end (grid_sdf reads c0 + 1 on every axis)
+    const size_t padded = n + (size_t)sy * sz + sz + 1;
+    void *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, padded * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemset(static_cast<float *>(d) + n, 0, (padded - n) * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(d, values, n * sizeof(float), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      if (d) cudaFree(d);
+      scene_free(s);
+      return cuda_fail(e, "grid upload");
+    }
+    adopt(s, d, padded * sizeof(float));
+    s->bytes += n * sizeof(float);
+    g.values = static_cast<const float *>(d);
   }
   if (rc == RT_OK) rc = scene_finish(s, out);
   if (rc != RT_OK) scene_free(s);

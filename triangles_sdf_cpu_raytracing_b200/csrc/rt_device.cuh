@@ -167,8 +167,18 @@ __device__ __forceinline__ uint32_t grid_offz(uint32_t z) {
 }
 
 // SDFGrid::sdf(float3), grid_raytracing.cpp:7-62; cell = (c0x, c0y, c0z) packed by the caller when it wants the
-// grid's "prim id".  ceil(p) is evaluated as floor(p) + (p != floor(p)), the same value for 0 <= p < 2^23.
-// (A real branch for the c1 == c0 case instead of the selects below was measured and rejected: the case is not rare,
+// grid's "prim id".
+// LINEAR layout: the reference's integer-coordinate special case (:25-38: ceil == floor on an axis -> weights (1, 0),
+// both corners the same sample) needs no code.  With c1 = c0 + 1 always, the natural weights on such an axis are
+// p - c0 = 0 and c1 - p = 1, both exact: the four corners at c0 carry weight 1 where the reference's four (identical)
+// corners at "c1" did, so the same four products come out bit for bit, in the same relative order, and the other four
+// terms are (finite sample) x 0 = +-0 where the reference's were +-0 too.  Adding +-0 never changes a non-zero partial
+// sum, and a sum that starts at +0 cannot become -0, so the result is the same float.  Needs: finite samples (checked
+// at upload; grids with infinities take the literal BRICKS path) and readable memory one slab + one row + one sample
+// past the end (the upload pads with zeros).  Saves the three compares and twelve selects per sample, and the z + 1
+// loads become immediate offsets of the z loads.
+// BRICKS layout: literal form.  ceil(p) is evaluated as floor(p) + (p != floor(p)), the same value for 0 <= p < 2^23.
+// (A real branch for the c1 == c0 case instead of the selects was measured and rejected: the case is not rare,
 // every ray's first sample sits exactly on the box face it entered through; grid 4K 0.338 -> 0.373 ms.)
 template <bool BRICKS, bool COUNT>
 __device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell, Counters &cnt) {
@@ -178,22 +188,34 @@ __device__ __forceinline__ float grid_sdf(const GridDev &g, V3 p, uint32_t &cell
   p.x = (p.x + 1.0f) * g.hfx; p.y = (p.y + 1.0f) * g.hfy; p.z = (p.z + 1.0f) * g.hfz;
   const float c0fx = floorf(p.x), c0fy = floorf(p.y), c0fz = floorf(p.z);
   const uint32_t c0x = (uint32_t)c0fx, c0y = (uint32_t)c0fy, c0z = (uint32_t)c0fz;
-  const bool ix = p.x != c0fx, iy = p.y != c0fy, iz = p.z != c0fz;  // c1 != c0 on that axis
-  const float c1fx = ix ? c0fx + 1.0f : c0fx, c1fy = iy ? c0fy + 1.0f : c0fy, c1fz = iz ? c0fz + 1.0f : c0fz;
-  float px = p.x - c0fx, py = p.y - c0fy, pz = p.z - c0fz;  // p_c0f
-  float qx = c1fx - p.x, qy = c1fy - p.y, qz = c1fz - p.z;  // c1f_p
-  if (!ix) { px = 1.0f; qx = 0.0f; }                        // :25-38
-  if (!iy) { py = 1.0f; qy = 0.0f; }
-  if (!iz) { pz = 1.0f; qz = 0.0f; }
-  const uint32_t x0 = grid_offx<BRICKS>(g, c0x), x1 = ix ? grid_offx<BRICKS>(g, c0x + 1u) : x0;
-  const uint32_t y0 = grid_offy<BRICKS>(g, c0y), y1 = iy ? grid_offy<BRICKS>(g, c0y + 1u) : y0;
-  const uint32_t z0 = grid_offz<BRICKS>(c0z), z1 = iz ? grid_offz<BRICKS>(c0z + 1u) : z0;
-  const float *v = g.values;
-  const uint32_t a00 = x0 + y0, a01 = x0 + y1, a10 = x1 + y0, a11 = x1 + y1;
-  const float v0 = __ldg(v + (a00 + z0)), v1 = __ldg(v + (a00 + z1));
-  const float v2 = __ldg(v + (a01 + z0)), v3 = __ldg(v + (a01 + z1));
-  const float v4 = __ldg(v + (a10 + z0)), v5 = __ldg(v + (a10 + z1));
-  const float v6 = __ldg(v + (a11 + z0)), v7 = __ldg(v + (a11 + z1));
+  float v0, v1, v2, v3, v4, v5, v6, v7, px, py, pz, qx, qy, qz;
+  if (!BRICKS) {
+    px = p.x - c0fx; py = p.y - c0fy; pz = p.z - c0fz;                             // p_c0f
+    qx = (c0fx + 1.0f) - p.x; qy = (c0fy + 1.0f) - p.y; qz = (c0fz + 1.0f) - p.z;  // c1f_p
+    const float *v00 = g.values + ((c0x * g.stride_x + c0y * g.stride_y) + c0z);
+    const float *v01 = v00 + g.stride_y, *v10 = v00 + g.stride_x, *v11 = v10 + g.stride_y;
+    v0 = __ldg(v00); v1 = __ldg(v00 + 1);
+    v2 = __ldg(v01); v3 = __ldg(v01 + 1);
+    v4 = __ldg(v10); v5 = __ldg(v10 + 1);
+    v6 = __ldg(v11); v7 = __ldg(v11 + 1);
+  } else {
+    const bool ix = p.x != c0fx, iy = p.y != c0fy, iz = p.z != c0fz;  // c1 != c0 on that axis
+    const float c1fx = ix ? c0fx + 1.0f : c0fx, c1fy = iy ? c0fy + 1.0f : c0fy, c1fz = iz ? c0fz + 1.0f : c0fz;
+    px = p.x - c0fx; py = p.y - c0fy; pz = p.z - c0fz;  // p_c0f
+    qx = c1fx - p.x; qy = c1fy - p.y; qz = c1fz - p.z;  // c1f_p
+    if (!ix) { px = 1.0f; qx = 0.0f; }                  // :25-38
+    if (!iy) { py = 1.0f; qy = 0.0f; }
+    if (!iz) { pz = 1.0f; qz = 0.0f; }
+    const uint32_t x0 = grid_offx<BRICKS>(g, c0x), x1 = ix ? grid_offx<BRICKS>(g, c0x + 1u) : x0;
+    const uint32_t y0 = grid_offy<BRICKS>(g, c0y), y1 = iy ? grid_offy<BRICKS>(g, c0y + 1u) : y0;
+    const uint32_t z0 = grid_offz<BRICKS>(c0z), z1 = iz ? grid_offz<BRICKS>(c0z + 1u) : z0;
+    const float *v = g.values;
+    const uint32_t a00 = x0 + y0, a01 = x0 + y1, a10 = x1 + y0, a11 = x1 + y1;
+    v0 = __ldg(v + (a00 + z0)); v1 = __ldg(v + (a00 + z1));
+    v2 = __ldg(v + (a01 + z0)); v3 = __ldg(v + (a01 + z1));
+    v4 = __ldg(v + (a10 + z0)); v5 = __ldg(v + (a10 + z1));
+    v6 = __ldg(v + (a11 + z0)); v7 = __ldg(v + (a11 + z1));
+  }
   float res = 0.0f;
   res += v0 * qx * qy * qz;
   res += v1 * qx * qy * pz;

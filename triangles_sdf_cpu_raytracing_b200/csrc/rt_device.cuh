@@ -250,8 +250,28 @@ constexpr uint32_t GRID_PREFETCH_AFTER = 32;
 // the iteration each of them happens to hit.
 // PREFETCH: the flavour the small-launch (HEAVY) kernels use.  Measured: one GPU's eighth of the 4K 513^3 frame 0.086 ->
 // 0.077 ms; on full frames the extra counter costs the register-tight loop 2-5 %, so they keep the plain flavour.
-template <bool BRICKS, bool COUNT, bool PREFETCH = false>
-__device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+template <bool BRICKS, bool COUNT, bool PREFETCH = false, bool PIN = false>
+__device__ __forceinline__ Hit grid_intersect(const GridDev &g0, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
+  // PIN: the seven launch constants of the march loop (scale, strides, base pointer) are made to look per-thread (a
+  // select on a condition the compiler cannot decide), so that they stay in vector registers.  Left alone, ptxas keeps
+  // them in uniform registers and copies each one into a vector register again at every use: seven MOVs in a
+  // 94-instruction loop.  The kernel still fits its 48 registers.  Measured (profiles/r2_grid_loop.txt): 513^3 grid 4K
+  // 0.327 -> 0.303 ms, one GPU's eighth of it 0.081 -> 0.070; the out-of-line copy the secondary rays call loses 4 %
+  // with it and keeps the plain form.
+#ifdef __CUDA_ARCH__
+  constexpr bool PINNED = PIN && !BRICKS;
+  GridDev gp;
+  if (PINNED) {
+    const bool never = d.x != d.x;
+    gp = g0;
+    gp.hfx = never ? g0.hfy : g0.hfx; gp.hfy = never ? g0.hfz : g0.hfy; gp.hfz = never ? g0.hfx : g0.hfz;
+    gp.stride_x = never ? g0.stride_y : g0.stride_x; gp.stride_y = never ? g0.stride_x : g0.stride_y;
+    gp.values = never ? g0.values + 1 : g0.values;  // (every alternative is harmless: a NaN direction never samples)
+  }
+  const GridDev &g = PINNED ? gp : g0;
+#else
+  const GridDev &g = g0;
+#endif
   Hit r = hit_none();
   V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   float t1, t2;
@@ -261,10 +281,11 @@ __device__ __forceinline__ Hit grid_intersect(const GridDev &g, V3 o, V3 d, floa
   V3 p = along(o, d, t);
   p.x = std_max(p.x, -1.0f); p.y = std_max(p.y, -1.0f); p.z = std_max(p.z, -1.0f);
   p.x = std_min(p.x, 1.0f); p.y = std_min(p.y, 1.0f); p.z = std_min(p.z, 1.0f);
-  // (the six bound tests as one `max(|x|, |y|, |z|) <= 1` and a cell index recomputed after the loop were measured:
-  // 1080p 0.112 -> 0.139 ms, 513^3 4K 0.366 -> 0.395 ms; the compiler's loop with the six compares is the better one)
+  // (one `max(|x|, |y|, |z|) <= 1` and a cell index recomputed after the loop were measured: 1080p 0.112 -> 0.139 ms,
+  // 513^3 4K 0.366 -> 0.395 ms; three compares on |x|, |y|, |z| instead of the six: 0.331 -> 0.327 ms)
   uint32_t steps = 0;
-  while (p.x <= 1.0f && p.y <= 1.0f && p.z <= 1.0f && p.x >= -1.0f && p.y >= -1.0f && p.z >= -1.0f) {
+  // |x| <= 1 is the reference's pair of tests (-1 <= x && x <= 1, false for a NaN either way) in one compare
+  while (fabsf(p.x) <= 1.0f && fabsf(p.y) <= 1.0f && fabsf(p.z) <= 1.0f) {
     uint32_t cell;
     float sd = grid_sdf<BRICKS, COUNT>(g, p, cell, cnt);
     if (sd < 1e-3f) {

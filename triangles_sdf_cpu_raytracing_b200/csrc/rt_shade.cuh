@@ -7,22 +7,23 @@ constexpr int KIND_GRID = 0, KIND_OCTREE = 1, KIND_BVH = 2, KIND_BRUTE = 3, KIND
 constexpr int KIND_GRID_PF = 5;  // the linear grid with prefetch along long marches (small launches, rt_device.cuh)
 
 // IScene::intersect of the model, and of SceneUnion(model, plane) (raytracing.hpp:83-97)
-template <int KIND, bool COUNT>
+// PIN: the inlined primary-ray call (rt_device.cuh, grid_intersect)
+template <int KIND, bool COUNT, bool PIN = false>
 __device__ __forceinline__ Hit model_intersect(const SceneDev &s, const float4 *smemTris, V3 o, V3 d, float tNear,
                                                float tFar, Counters &cnt) {
   if (COUNT) cnt.rays++;
-  if (KIND == KIND_GRID) return grid_intersect<false, COUNT>(s.grid, o, d, tNear, tFar, cnt);
-  if (KIND == KIND_GRID_PF) return grid_intersect<false, COUNT, true>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_GRID) return grid_intersect<false, COUNT, false, PIN>(s.grid, o, d, tNear, tFar, cnt);
+  if (KIND == KIND_GRID_PF) return grid_intersect<false, COUNT, true, PIN>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_GRID_BRICKS) return grid_intersect<true, COUNT>(s.grid, o, d, tNear, tFar, cnt);
   if (KIND == KIND_OCTREE) return oct_intersect<COUNT>(s.oct, o, d, tNear, tFar, cnt);
   if (KIND == KIND_BVH) return bvh_intersect<COUNT>(s.mesh, o, d, tNear, tFar, cnt);
   return brute_intersect<COUNT>(s.mesh, smemTris, o, d, tNear, tFar, cnt);
 }
 
-template <int KIND, bool COUNT>
+template <int KIND, bool COUNT, bool PIN = false>
 __device__ __forceinline__ Hit scene_intersect(const SceneDev &s, const float4 *smemTris, bool hasPlane, float planeY,
                                                V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
-  Hit a = model_intersect<KIND, COUNT>(s, smemTris, o, d, tNear, tFar, cnt);
+  Hit a = model_intersect<KIND, COUNT, PIN>(s, smemTris, o, d, tNear, tFar, cnt);
   if (!hasPlane) return a;
   Hit b = plane_intersect(planeY, o, d, tNear, tFar);
   return (a.t < b.t) ? a : b;
@@ -88,7 +89,7 @@ __device__ __forceinline__ bool intersection_color(const SceneDev &s, const Fram
   const bool plane = f.has_plane != 0;
   Hit hit = SECONDARY ? scene_intersect_shared<KIND, COUNT>(s, smemTris, plane, f.plane_y, o, d, f.t_near,
                                                            std_min(f.t_far, tPrev), cnt)
-                      : scene_intersect<KIND, COUNT>(s, smemTris, plane, f.plane_y, o, d, f.t_near,
+                      : scene_intersect<KIND, COUNT, true>(s, smemTris, plane, f.plane_y, o, d, f.t_near,
                                                      std_min(f.t_far, tPrev), cnt);
   if (!hit.hitten) return false;
   if (COUNT) cnt.hits++;

@@ -615,7 +615,9 @@ __device__ __forceinline__ Hit oct_intersect(const OctreeDev &oc, V3 o, V3 d, fl
     closedMask = cf ? 1u : 0u;
 #endif
     // (A "while-while" form, all lanes walking to their next surface leaf before any of them marches, was measured
-    // and rejected: octree6 4K 0.73 -> 0.75 ms, depth-8 stand-in 1.16 -> 1.34 ms; profiles/r1_tune.txt.)
+    // and rejected: octree6 4K 0.73 -> 0.75 ms, depth-8 stand-in 1.16 -> 1.34 ms; profiles/r1_tune.txt.  So was the
+    // milder form of round 2, a lane parking its leaf until n = 4 .. 24 lanes of the warp can march together:
+    // 1.058 -> 1.08 .. 1.17 ms, profiles/r2_octree_variants.txt.)
     for (;;) {
       if (w == 0) {
         // ---- back to the parent

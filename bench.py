@@ -635,7 +635,10 @@ def run_cuda(args):
     #     stopwatch brackets draw, not the clear.  The kernels bulk-load each tile's previous depth, leave tiles without a
     #     nearer hit alone, and store the others (fetching the previous colour only for partly hit tiles).
     inout = mk(c["rayPos"], c["viewInv"])
+    xfer0 = scene_n.transfer_bytes()
     e2e_ms, e2e_kms = time_host(inout, host_clear)
+    xfer1 = scene_n.transfer_bytes()
+    xfer_calls = n_e2e + 3
     inout_chk_c = hc.numpy().view(np.uint32).reshape(H, W).copy()
     inout_chk_t = ht.numpy().reshape(H, W).copy()
     # the same with the host-side clear inside the stopwatch (what a frame of the viewer's loop costs the caller)
@@ -660,15 +663,22 @@ def run_cuda(args):
     n_keep, n_e2e = n_e2e, max(3, n_e2e // 3)
     pageable_ms, _ = time_host(inout, page_clear, pc, pt)
     n_e2e = n_keep
-    # bytes that cross PCIe per in/out frame, from the frame itself: 32 x 4-pixel tiles, depth in for all of them, colour
-    # + depth out for tiles with a hit, colour in as well for partly hit ones
+    # bytes that cross PCIe per in/out frame: counted by the kernels themselves as they issue the bulk copies
+    # (rt_scene_transfer_bytes): previous depth in for the 32 x 4-pixel tiles in which a ray hits anything (a tile is
+    # first traced against a cleared depth: no hit then means no hit with any previous depth, and nothing is fetched),
+    # colour + depth out for tiles with a nearer hit, previous colour in as well for partly hit ones.  Cross-checked
+    # against the frame: the stored bytes must be exactly 8 B x 128 pixels x the tiles that hold a hit.
     Hp, Wp = (H + 3) // 4 * 4, (W + 31) // 32 * 32
     hm = np.zeros((Hp, Wp), bool)
     hm[:H, :W] = np.isfinite(chk_t)
     per_tile = hm.reshape(Hp // 4, 4, Wp // 32, 32).sum(axis=(1, 3))
     touched, partial = int((per_tile > 0).sum()), int(((per_tile > 0) & (per_tile < 128)).sum())
-    h2d = 4 * px + partial * 128 * 4 + C.sizeof(L.RtFrame) * n_dev
-    d2h = touched * 128 * 8
+    fetched, stored = (xfer1[0] - xfer0[0]) // xfer_calls, (xfer1[1] - xfer0[1]) // xfer_calls
+    if W % 32 == 0 and H % 4 == 0 and stored != touched * 128 * 8:
+        raise SystemExit(f"transfer accounting: {stored} bytes stored per frame, the frame has {touched} tiles with a hit")
+    depth_tiles = (fetched - partial * 128 * 4) // (128 * 4)
+    h2d = fetched + C.sizeof(L.RtFrame) * n_dev
+    d2h = stored
     pcie_peak = 56.0 * n_dev
     e2e = {"value": px / e2e_ms / 1e3, "unit": "Mrays/s", "ms_per_step": e2e_ms, "n_gpus": n_dev,
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "device_ms_slowest_gpu": e2e_kms,
@@ -678,10 +688,13 @@ def run_cuda(args):
                   + (f"; rt_init lists {n_dev} devices: the scene is replicated and the call fans interleaved 8-row "
                      f"bands out over them from this one process" if n_dev > 1 else ""),
            "transfer": "every GPU's render kernel works on the pinned host framebuffer over its own PCIe link with 128-byte "
-                       "bulk copies: previous depth of each tile in, colour + depth of tiles with a nearer hit out "
-                       "(previous colour in only for partly hit tiles); one launch per GPU, no device framebuffer, no "
-                       "copy engine",
-           "tiles": {"of_32x4_pixels": int(per_tile.size), "with_a_hit": touched, "partly_hit": partial},
+                       "bulk copies: a tile is traced against a cleared depth first; only if a ray hits is its previous "
+                       "depth fetched (pixels it bounds nearer than tFar are traced again with it, as the reference would "
+                       "have), colour + depth of tiles with a nearer hit go out (previous colour in only for partly hit "
+                       "tiles); one launch per GPU, no device framebuffer, no copy engine; bytes counted by the kernels "
+                       "(rt_scene_transfer_bytes)",
+           "tiles": {"of_32x4_pixels": int(per_tile.size), "depth_fetched": int(depth_tiles), "with_a_hit": touched,
+                     "partly_hit": partial},
            "link": {"bound": "pcie", "achieved": max(h2d, d2h) / (e2e_ms * 1e-3) / 1e9, "peak": pcie_peak, "unit": "GB/s",
                     "frac": max(h2d, d2h) / (e2e_ms * 1e-3) / 1e9 / pcie_peak,
                     "peak_is": f"{n_dev} x 56 GB/s per direction (copy-engine rate of one Gen5 x16 link, tools/pcie_probe.py); "

@@ -164,6 +164,12 @@ int rt_scene_replicas(const rt_scene *scene, int *devices, int cap); /* -> numbe
 /* bytes of scene data resident in HBM, and the model's bounding box (meshes: calc_bbox, raytracing.hpp:22-37;
  * SDF scenes: [-1,1]^3) */
 int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]);
+/* Transfer accounting of the in/out framebuffer contract (rt_render_host on pinned buffers, rt_render_device on a peer
+ * framebuffer): running totals, since the scene was created and over all its devices, of the framebuffer bytes the render
+ * kernels fetched (previous depth of the 32 x 4-pixel tiles in which a ray hits anything at all; previous colour / prim ids
+ * of partly hit tiles) and stored (colour + depth [+ prim ids] of tiles with a nearer hit).  Synchronises with the scene's devices.
+ * Any output pointer may be NULL. */
+int rt_scene_transfer_bytes(const rt_scene *scene, uint64_t *fetched, uint64_t *stored);
 
 /* ---- options (process-wide defaults; reads are racy by design, set them before rendering) ------- */
 int rt_set_math_mode(int mode /*rt_math_mode*/);
@@ -186,8 +192,10 @@ int rt_render_device(const rt_scene *scene, const rt_frame *frame, uint32_t *col
  * 16-byte aligned (anything else silently takes the copies), W % 8 == 0 (band_rows % 4 == 0 for a banded call) and
  * counters is NULL, the kernel works on the caller's buffers directly over PCIe, for every scene kind and shading mode
  * (secondary rays and the ground plane included): with rt_frame.clear = 1 it stores its tiles as 128-byte bulk stores;
- * with clear = 0 (the reference's in/out framebuffer) it first fetches each tile's previous contents with bulk loads and
- * stores the merged tile back.  No device framebuffer, no copy engine; *device_ms then equals *total_ms.  Pageable
+ * with clear = 0 (the reference's in/out framebuffer) a 32 x 4-pixel tile in which no ray hits anything is left alone
+ * without being read; of the others the previous depth is fetched with bulk loads (it bounds the rays, raytracing.cpp:17),
+ * of partly hit ones the previous colour as well, and the merged tile is stored back (rt_scene_transfer_bytes counts
+ * both directions).  No device framebuffer, no copy engine; *device_ms then equals *total_ms.  Pageable
  * buffers and workload counters go through the pipelined copies.  On a scene replicated by rt_init every listed GPU
  * does this for its own bands over its own PCIe link. */
 int rt_render_host(const rt_scene *scene, const rt_frame *frame, uint32_t *color, float *t_inout, uint32_t *prim,

@@ -53,6 +53,28 @@ def check_scene(key, s, tag):
     host_call(s, rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), color, t)
     assert util.same_bits(tn[:, :W // 2], c["t"][:, :W // 2]) and np.array_equal(cn[:, :W // 2], c["color_normal"][:, :W // 2]), (tag, key, "pinned in/out")
     assert np.all(cn[:, W // 2:] == 7) and np.all(tn[:, W // 2:] == np.float32(1e-3)), (tag, key, "nearer depth survives")
+    # --- pinned in/out over a pre-filled depth (golden), with the transfer accounting of that one call: stored = the
+    #     tiles (32 x 4 pixels) that changed, fetched = at least their depth and at most every tile's depth + the colour
+    #     of the partly changed ones (tiles no ray can reach the model's bounds in are not even read)
+    cn[...] = 0x11223344; tn[...] = 2.2
+    f0, s0 = s.transfer_bytes()
+    host_call(s, rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H), color, t)
+    f1, s1 = s.transfer_bytes()
+    if not is_mesh or c["scene"] == "cube":
+        assert util.same_bits(tn, c["t_prefilled"]) and np.array_equal(cn, c["color_prefilled"]), (tag, key, "pinned prefilled")
+    if W % 32 == 0:
+        changed = tn != np.float32(2.2)
+        stored = fetched_min = fetched_max = 0
+        for y0 in range(0, H, 4):
+            rows = min(4, H - y0)
+            for x0 in range(0, W, 32):
+                n = int(changed[y0:y0 + rows, x0:x0 + 32].sum())
+                stored += rows * 32 * 8 if n else 0
+                fetched_min += rows * 32 * 4 * ((1 if n else 0) + (1 if 0 < n < rows * 32 else 0))
+                fetched_max += rows * 32 * 4 * (1 + (1 if 0 < n < rows * 32 else 0))
+        assert s1 - s0 == stored and fetched_min <= f1 - f0 <= fetched_max, (tag, key, "transfer bytes", f1 - f0, s1 - s0, stored, fetched_min, fetched_max)
+        if c["scene"] == "cube":
+            assert f1 - f0 < fetched_max, (tag, key, "tiles off the model are not fetched", f1 - f0, fetched_max)
     # --- pinned prim ids: equal to what the copy pipeline returns (counters force the copies)
     prim = pinned(H, W, torch.int32, 0x33333333)
     host_call(s, rt.make_frame(c["rayPos"], c["viewInv"], c["projInv"], W, H, clear=True), color, t, prim=prim)

@@ -60,6 +60,7 @@ SIGNATURES = {
     "rt_scene_kind_of": (_i, [_vp]),
     "rt_scene_device": (_i, [_vp]),
     "rt_scene_info": (_i, [_vp, C.POINTER(C.c_uint64), C.POINTER(_f), C.POINTER(_f)]),
+    "rt_scene_transfer_bytes": (_i, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rt_set_math_mode": (_i, [_i]),
     "rt_set_sched_mode": (_i, [_i]),
     "rt_render_device": (_i, [_vp, C.POINTER(RtFrame), _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -102,6 +102,12 @@ class Scene:
         L.check(L.lib().rt_scene_info(self._h, C.byref(b), lo, hi))
         return dict(device_bytes=int(b.value), bbox_min=np.array(lo[:], np.float32), bbox_max=np.array(hi[:], np.float32))
 
+    def transfer_bytes(self):
+        """Running (fetched, stored) framebuffer bytes of the in/out calls on pinned / peer buffers (rt_scene_transfer_bytes)."""
+        f, s = C.c_uint64(), C.c_uint64()
+        L.check(L.lib().rt_scene_transfer_bytes(self._h, C.byref(f), C.byref(s)))
+        return int(f.value), int(s.value)
+
     def replicas(self):
         """Devices that hold a copy of the scene (rt_init)."""
         d = np.zeros(64, np.int32)

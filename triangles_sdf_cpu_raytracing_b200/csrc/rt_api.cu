@@ -78,6 +78,7 @@ struct Replica {
   std::vector<std::pair<void *, size_t>> allocs;  // device allocations and their sizes (cloned onto the other devices)
   uint32_t *tile_counters = nullptr;              // ring, one per in-flight persistent launch
   std::atomic<uint32_t> next_counter{0};
+  unsigned long long *xfer = nullptr;             // running {fetched, stored} bytes of the in/out staged tiles
   // per-device state of rt_render_host / of a fanned-out rt_render_device
   uint32_t *h_color = nullptr;  // device framebuffer of the copy pipeline (allocated on first use)
   float *h_t = nullptr;
@@ -147,10 +148,12 @@ void adopt(rt_scene *s, void *d, size_t bytes) { s->reps[0]->allocs.emplace_back
 
 int finish_replica(Replica &r) {
   void *d = nullptr;
-  RT_CUDA(cudaMalloc(&d, N_TILE_COUNTERS * sizeof(uint32_t)));
-  r.allocs.emplace_back(d, N_TILE_COUNTERS * sizeof(uint32_t));
+  const size_t bytes = N_TILE_COUNTERS * sizeof(uint32_t) + 2 * sizeof(unsigned long long);
+  RT_CUDA(cudaMalloc(&d, bytes));
+  r.allocs.emplace_back(d, bytes);
   r.tile_counters = static_cast<uint32_t *>(d);
-  RT_CUDA(cudaMemset(d, 0, N_TILE_COUNTERS * sizeof(uint32_t)));
+  r.xfer = reinterpret_cast<unsigned long long *>(r.tile_counters + N_TILE_COUNTERS);
+  RT_CUDA(cudaMemset(d, 0, bytes));
   RT_CUDA(cudaDeviceSynchronize());
   return RT_OK;
 }
@@ -473,6 +476,21 @@ int rt_scene_replicas(const rt_scene *scene, int *devices, int cap) {
   return (int)scene->reps.size();
 }
 
+int rt_scene_transfer_bytes(const rt_scene *scene, uint64_t *fetched, uint64_t *stored) {
+  if (!scene) return fail(RT_ERR_INVALID, "null scene");
+  uint64_t f = 0, st = 0;
+  for (const auto &rep : scene->reps) {
+    DeviceGuard dg(rep->device);
+    unsigned long long v[2] = {0, 0};
+    RT_CUDA(cudaMemcpy(v, rep->xfer, sizeof(v), cudaMemcpyDeviceToHost));
+    f += v[0];
+    st += v[1];
+  }
+  if (fetched) *fetched = f;
+  if (stored) *stored = st;
+  return RT_OK;
+}
+
 int rt_scene_info(const rt_scene *scene, uint64_t *device_bytes, float bbox_min[3], float bbox_max[3]) {
   if (!scene) return fail(RT_ERR_INVALID, "scene is null");
   if (device_bytes) *device_bytes = scene->bytes;
@@ -644,6 +662,7 @@ int render_on_stream(const rt_scene *scene, Replica &rep, const FrameDev &fd, ui
   a.tile_counter = rep.tile_counters + (rep.next_counter.fetch_add(1) % N_TILE_COUNTERS);
   a.tile_block = g_env_tile_block;
   a.stage_stores = 0;
+  a.xfer = rep.xfer;
   int sched = resolve_sched(scene);
   if ((fd.clear || store == STORE_INOUT) && staged_kernel_available(fd, counters_dev) &&
       (store >= 0 ? store >= STORE_STAGED : g_env_stage != 0)) {

@@ -247,32 +247,39 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
 #pragma unroll
   for (uint32_t r = 0; r < 4u; ++r)
     if (v0 + r < f.rows_here && band_row(f, v0 + r) < f.H) ++rowsHere;
-  if (INOUT) {
-    // the previous DEPTH of the tile is all a ray needs (tPrev bounds it); colour and prim ids are only fetched later,
-    // and only if the tile ends up partly hit (a tile with no nearer hit is not touched at all, a fully hit one is
-    // overwritten whole)
-    if (threadIdx.x == 0) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowsHere * rowBytes) : "memory");
-      load_rows(a.t_in, (uint32_t)__cvta_generic_to_shared(&sDepth[0][0]));
-    }
-    wait_phase(0);
-  }
-  Counters cnt = {};
-  bool inFrame = false, hit = false;
-  uint32_t myColor = 0u, myPrim = RT_PRIM_MISS;
-  float myT = __int_as_float(0x7f800000);
+  // this thread's pixel and eye ray
+  bool inFrame = false;
+  const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
+  V3 d = mk3(0.0f, 0.0f, 0.0f);
   if (x < f.W && v < f.rows_here) {
     const uint32_t row = band_row(f, v);
     if (row < f.H) {
       inFrame = true;
-      const V3 o = mk3(f.ray_pos[0], f.ray_pos[1], f.ray_pos[2]);
-      const V3 d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
-      const float tPrev = INOUT ? sDepth[ly][lx] : __int_as_float(0x7f800000);
+      d = eye_ray(f, (int)x, (int)(f.H - 1u - row));
+    }
+  }
+  Counters cnt = {};
+  bool hit = false;
+  uint32_t myColor = 0u, myPrim = RT_PRIM_MISS;
+  float myT = __int_as_float(0x7f800000);
+  // INOUT: the previous depth only enters the reference's draw as the ray's far bound min(tFar, tPrev)
+  // (raytracing.cpp:17), and every intersector only ever REJECTS more with a nearer far bound (the bound clips box
+  // windows; no march, triangle test or visit order starts from it).  So the tile is first traced as if its previous
+  // depth were +inf, what FrameBuffer::clear leaves there (src/main.cpp:197): if no ray hits then, none can with the
+  // true depth, and the tile is left alone before anything has crossed the link.  Otherwise the previous depth is
+  // fetched; pixels where it is nearer than tFar (a framebuffer that was not cleared) are traced again with the true
+  // bound, exactly as the reference would have.
+#pragma unroll 1
+  for (int pass = 0; pass < (INOUT ? 2 : 1); ++pass) {
+    float tPrev = __int_as_float(0x7f800000);
+    bool trace = inFrame;
+    if (pass == 1) {
+      tPrev = inFrame ? sDepth[ly][lx] : tPrev;
+      trace = inFrame && tPrev < f.t_far;
+      if (!__syncthreads_or(trace)) break;
+      if (trace) hit = false;
+    }
+    if (trace) {
       C4 col;
       float tNew = __int_as_float(0x7f800000);
       uint32_t prim;
@@ -284,6 +291,23 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
         myT = tNew;
         myPrim = prim;
       }
+    }
+    if (INOUT && pass == 0) {
+      if (!__syncthreads_or(hit)) {
+        if (HEAVY) heavy_report(a.heavy, hb);
+        return;
+      }
+      if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowsHere * rowBytes) : "memory");
+        load_rows(a.t_in, (uint32_t)__cvta_generic_to_shared(&sDepth[0][0]));
+        if (a.xfer) atomicAdd(a.xfer, (unsigned long long)(rowsHere * rowBytes));
+      }
+      wait_phase(0);
     }
   }
   if (INOUT) {
@@ -299,6 +323,7 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
                      : "memory");
         load_rows(a.color, (uint32_t)__cvta_generic_to_shared(&sColor[0][0]));
         if (wantPrim) load_rows(a.prim, (uint32_t)__cvta_generic_to_shared(&sPrim[0][0]));
+        if (a.xfer) atomicAdd(a.xfer, (unsigned long long)(rowsHere * (wantPrim ? 2u : 1u) * rowBytes));
       }
       wait_phase(1);
     }
@@ -332,6 +357,7 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
                      "r"((uint32_t)__cvta_generic_to_shared(&sPrim[threadIdx.x][0])), "r"(rowBytes)
                      : "memory");
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      if (INOUT && a.xfer) atomicAdd(a.xfer + 1, (unsigned long long)((wantPrim ? 3u : 2u) * rowBytes));
       // the shared-memory rows must stay valid until the bulk engine has read them; the writes themselves complete
       // before the grid does
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");

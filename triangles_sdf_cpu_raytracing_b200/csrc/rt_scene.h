@@ -140,6 +140,7 @@ struct RenderArgs {
   unsigned long long *counters;  // rt_counters as 9 x u64, or null
   uint32_t *tile_counter;        // persistent scheduling: next tile to hand out
   int32_t stage_stores;          // tiles: stage the tile in shared memory, store it with TMA (1: fused clear, 2: in/out)
+  unsigned long long *xfer;      // in/out staged tiles: running byte counts {fetched, stored} (rt_scene_transfer_bytes), or null
   int32_t tile_block;            // RT_SCHED_TILES: threads per block (32, 64, 128, 256)
   int32_t oct_refill_min, oct_leaf_batch;  // RT_SCHED_COMPACT: idle lanes needed for a refill, leaf lanes for a march
 };

@@ -667,14 +667,14 @@ def run_cuda(args):
     # (rt_scene_transfer_bytes): previous depth in for the 32 x 4-pixel tiles in which a ray hits anything (a tile is
     # first traced against a cleared depth: no hit then means no hit with any previous depth, and nothing is fetched),
     # colour + depth out for tiles with a nearer hit, previous colour in as well for partly hit ones.  Cross-checked
-    # against the frame: the stored bytes must be exactly 8 B x 128 pixels x the tiles that hold a hit.
+    # against the frame: the stored bytes must be 8 B x 128 pixels x the tiles that hold a hit.
     Hp, Wp = (H + 3) // 4 * 4, (W + 31) // 32 * 32
     hm = np.zeros((Hp, Wp), bool)
     hm[:H, :W] = np.isfinite(chk_t)
     per_tile = hm.reshape(Hp // 4, 4, Wp // 32, 32).sum(axis=(1, 3))
     touched, partial = int((per_tile > 0).sum()), int(((per_tile > 0) & (per_tile < 128)).sum())
     fetched, stored = (xfer1[0] - xfer0[0]) // xfer_calls, (xfer1[1] - xfer0[1]) // xfer_calls
-    if W % 32 == 0 and H % 4 == 0 and stored != touched * 128 * 8:
+    if W % 32 == 0 and H % 4 == 0 and stored != touched * 1024:
         raise SystemExit(f"transfer accounting: {stored} bytes stored per frame, the frame has {touched} tiles with a hit")
     depth_tiles = (fetched - partial * 128 * 4) // (128 * 4)
     h2d = fetched + C.sizeof(L.RtFrame) * n_dev

@@ -119,13 +119,18 @@ __device__ __forceinline__ bool heavy_pick(const HeavySched &h, HeavyBlock &hb, 
   if ((threadIdx.x & 31u) == 0u) hb.t0[threadIdx.x >> 5] = (uint32_t)clock();
   if (blockIdx.y < h.extra_rows) {
     const uint32_t slot = blockIdx.y * tilesX + blockIdx.x;
-    if (threadIdx.x == 0) hb.tile = slot < min(__ldcg(h.prev_count), HEAVY_CAP) ? __ldcg(h.prev + slot) : 0xFFFFFFFFu;
+    if (threadIdx.x == 0) {
+      uint32_t tile = slot < min(__ldcg(h.prev_count), HEAVY_CAP) ? __ldcg(h.prev + slot) : 0xFFFFFFFFu;
+      // the claim is one atomic exchange on both sides, so a tile is rendered exactly once per launch (an in/out tile
+      // rendered twice could fetch its own first, half-landed result as "previous contents")
+      if (tile < nTiles && atomicExch(h.done + tile, h.tag) == h.tag) tile = 0xFFFFFFFFu;  // its regular block was faster
+      hb.tile = tile;
+    }
     __syncthreads();
     const uint32_t tile = hb.tile;
-    if (tile >= nTiles) return false;  // empty slot, or a list built for another frame geometry
+    if (tile >= nTiles) return false;  // empty slot, a list built for another frame geometry, or already taken
     byi = tile / tilesX;
     bx = tile - byi * tilesX;
-    if (threadIdx.x == 0) __stcg(h.done + tile, h.tag);
     return true;
   }
   byi = blockIdx.y - h.extra_rows;
@@ -134,7 +139,7 @@ __device__ __forceinline__ bool heavy_pick(const HeavySched &h, HeavyBlock &hb, 
   int taken = 0;
   if (threadIdx.x == 0) {
     hb.tile = tile;
-    taken = __ldcg(h.done + tile) == h.tag;
+    taken = atomicExch(h.done + tile, h.tag) == h.tag;
   }
   return !__syncthreads_or(taken);
 }
@@ -182,6 +187,22 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
   }
 }
 
+// one pixel of an in/out tile traced with its true previous depth (render_tiles_staged_kernel, INOUT)
+template <int K, bool SECONDARY>
+__device__ __noinline__ bool retrace_pixel(const SceneDev &scene, const FrameDev &f, const float4 *smemTris, V3 o, V3 d,
+                                           float tPrev, uint32_t &color, float &t, uint32_t &prim) {
+  Counters cnt = {};
+  C4 col;
+  float tNew = __int_as_float(0x7f800000);
+  uint32_t pr;
+  if (!intersection_color<K, false, SECONDARY>(scene, f, smemTris, o, d, tPrev, col, tNew, pr, cnt) || isinf(tNew))
+    return false;
+  color = color_pack_rgba(col);
+  t = tNew;
+  prim = pr;
+  return true;
+}
+
 // ---- RT_SCHED_TILES with the tile staged in shared memory and stored by TMA (peer or pinned-host framebuffer) --------
 // When the framebuffer lives on ANOTHER GPU (peer access / CUDA IPC) or in page-locked HOST memory (rt_render_host), the
 // plain kernel's stores cross NVLink / PCIe as 32-byte pieces (one 8-pixel tile row per warp).  Here a block owns
@@ -191,12 +212,14 @@ __global__ void __launch_bounds__(32 * WX * WY, KIND == KIND_BVH ? 1024 / (32 * 
 // the bulk engine has READ its shared memory (wait_group.read), not until the writes have landed on the far side of
 // the link: the grid's completion covers that.  W % 8 == 0.
 //   INOUT = false: fused clear, every pixel of the tile is produced here.
-//   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile's previous DEPTH is first fetched
-//                  into shared memory by bulk loads completing on an mbarrier (it bounds every ray of the tile); a tile
-//                  without any nearer hit is then left alone, a fully hit one is stored whole, and only a partly hit
-//                  one fetches its previous colour (and prim ids) so that the rows that go back are complete.
+//   INOUT = true : the reference's in/out framebuffer (raytracing.cpp:90-94).  The tile is traced against a cleared depth
+//                  first; if nothing hits it is left alone unread.  Otherwise its previous DEPTH is fetched into shared
+//                  memory by bulk loads completing on an mbarrier and the pixels it bounds are traced again with it; a
+//                  tile without any nearer hit is then left alone, a fully hit one is stored whole, and only a partly
+//                  hit one fetches its previous colour (and prim ids) so that the rows that go back are complete.
+//                  (BVH: capped at 64 registers like the plain kernel; bunny 4K in/out call 0.434 -> 0.401 ms.)
 template <int KIND, bool INOUT, bool SECONDARY, bool HEAVY>
-__global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
+__global__ void __launch_bounds__(128, KIND == KIND_BVH ? 8 : 0) render_tiles_staged_kernel(const __grid_constant__ RenderArgs a) {
   extern __shared__ float4 smemTris[];
   __shared__ __align__(128) uint32_t sColor[4][32];
   __shared__ __align__(128) float sDepth[4][32];
@@ -268,46 +291,41 @@ __global__ void __launch_bounds__(128) render_tiles_staged_kernel(const __grid_c
   // depth were +inf, what FrameBuffer::clear leaves there (src/main.cpp:197): if no ray hits then, none can with the
   // true depth, and the tile is left alone before anything has crossed the link.  Otherwise the previous depth is
   // fetched; pixels where it is nearer than tFar (a framebuffer that was not cleared) are traced again with the true
-  // bound, exactly as the reference would have.
-#pragma unroll 1
-  for (int pass = 0; pass < (INOUT ? 2 : 1); ++pass) {
-    float tPrev = __int_as_float(0x7f800000);
-    bool trace = inFrame;
-    if (pass == 1) {
-      tPrev = inFrame ? sDepth[ly][lx] : tPrev;
-      trace = inFrame && tPrev < f.t_far;
-      if (!__syncthreads_or(trace)) break;
-      if (trace) hit = false;
+  // bound, exactly as the reference would have (retrace_pixel).
+  constexpr int K = (HEAVY && KIND == KIND_GRID) ? KIND_GRID_PF : KIND;
+  if (inFrame) {
+    C4 col;
+    float tNew = __int_as_float(0x7f800000);
+    uint32_t prim;
+    if (intersection_color<K, false, SECONDARY>(a.scene, f, smemTris, o, d, __int_as_float(0x7f800000), col, tNew, prim, cnt) &&
+        !isinf(tNew)) {
+      hit = true;
+      myColor = color_pack_rgba(col);
+      myT = tNew;
+      myPrim = prim;
     }
-    if (trace) {
-      C4 col;
-      float tNew = __int_as_float(0x7f800000);
-      uint32_t prim;
-      constexpr int K = (HEAVY && KIND == KIND_GRID) ? KIND_GRID_PF : KIND;
-      if (intersection_color<K, false, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, col, tNew, prim, cnt) &&
-          !isinf(tNew)) {
-        hit = true;
-        myColor = color_pack_rgba(col);
-        myT = tNew;
-        myPrim = prim;
-      }
+  }
+  if (INOUT) {
+    if (!__syncthreads_or(hit)) {  // no ray hits anything: nothing to fetch, nothing to store
+      if (HEAVY) heavy_report(a.heavy, hb);
+      return;
     }
-    if (INOUT && pass == 0) {
-      if (!__syncthreads_or(hit)) {
-        if (HEAVY) heavy_report(a.heavy, hb);
-        return;
-      }
-      if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      }
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowsHere * rowBytes) : "memory");
-        load_rows(a.t_in, (uint32_t)__cvta_generic_to_shared(&sDepth[0][0]));
-        if (a.xfer) atomicAdd(a.xfer, (unsigned long long)(rowsHere * rowBytes));
-      }
-      wait_phase(0);
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowsHere * rowBytes) : "memory");
+      load_rows(a.t_in, (uint32_t)__cvta_generic_to_shared(&sDepth[0][0]));
+      if (a.xfer) atomicAdd(a.xfer, (unsigned long long)(rowsHere * rowBytes));
+    }
+    wait_phase(0);
+    // a previous depth nearer than tFar (a framebuffer that was not cleared): that pixel again, with the true bound
+    // (out of line: the common path keeps the registers of a single trace)
+    if (inFrame) {
+      const float tPrev = sDepth[ly][lx];
+      if (tPrev < f.t_far) hit = retrace_pixel<K, SECONDARY>(a.scene, f, smemTris, o, d, tPrev, myColor, myT, myPrim);
     }
   }
   if (INOUT) {

@@ -116,7 +116,7 @@ struct FrameDev {
 // so every launch records which blocks ran long and the next launch of the same scene / frame geometry starts those
 // first: the grid carries extra leading rows of blocks that pick their tile from the previous launch's list; the
 // regular blocks skip tiles already taken that way.  Order only: every pixel is still rendered by exactly the same code
-// (a stale or racing list can cost redundant work, never a missing or half-rendered tile).
+// exactly once (both sides claim a tile with one atomic exchange; a stale list only costs the order).
 constexpr uint32_t HEAVY_CAP = 2048;
 struct HeavySched {
   const uint32_t *prev;        // tile ids (default-order block index) that ran long in the previous launch

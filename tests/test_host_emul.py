@@ -128,6 +128,41 @@ def test_device_source_on_cpu_in_out_depth_buffer(name):
     assert replaced > 0 and kept > 0
 
 
+@pytest.mark.parametrize("name,brute", (("example_grid", None), ("sdf_6", None), ("sdf_5", None), ("cube", None),
+                                        ("cube", True), ("spot", None), ("stanford-bunny", None)))
+def test_a_nearer_far_bound_only_rejects(name, brute):
+    """What the in/out tiles of render_tiles_staged_kernel rest on ("trace first, fetch later"): the
+    previous depth enters draw only as min(tFar, tPrev) (raytracing.cpp:17), so (a) a pixel that is not hit against a
+    cleared depth is not hit against ANY previous depth, and (b) a pixel whose previous depth is not below tFar comes out
+    exactly as against the cleared one.  The device source on the CPU, eyes inside the box / mesh included, with and
+    without the plane and the secondary rays."""
+    a = G.scene_arrays(name)
+    s = E.EmulScene.mesh(a["vpos4"], a["indices"], brute=brute) if "vpos4" in a else emul_scene(name)[0]
+    W, H = 48, 32
+    pinv = rt.host_projection(W, H)[1]
+    rng = np.random.default_rng(11)
+    changed = 0
+    for k, pos, vinv in seeded_cameras(16 if name in ("stanford-bunny", "spot") else 40, seed=203):
+        plane = k % 3 == 0
+        f = rt.make_frame(pos, vinv, pinv, W, H, mode=rt.SHADE_LAMBERT, shadows=plane, reflections=plane,
+                          plane_y=-1.0 if plane else None)
+        t0 = rng.choice(np.array([np.inf, 0.005, 0.011, 0.3, 0.9, 1.4, 2.0, 2.5, 3.1, 99.9, 100.0, 150.0], np.float32),
+                        size=(H, W)).astype(np.float32)
+        t0[rng.random((H, W)) < 0.15] = np.float32(np.nan)
+        c0 = rng.integers(1, 2**32, size=(H, W), dtype=np.uint32)
+        col_c, t_c, prim_c, _ = s.render(f, count=False)                      # cleared: colour 0, depth +inf
+        col_p, t_p, prim_p, _ = s.render(f, color=c0, t=t0, count=False)
+        hit_c = np.isfinite(t_c)
+        touched = (t_p.view(np.uint32) != t0.view(np.uint32)) | (col_p != c0)
+        assert not np.any(touched & ~hit_c), f"{name} camera {k}: a pixel without a hit against the cleared depth changed"
+        far = ~(t0 < np.float32(100.0))                                       # inf, 100, 150, NaN: min(tFar, tPrev) = tFar
+        same = (t_p.view(np.uint32) == t_c.view(np.uint32)) & (col_p == col_c) & (prim_p == prim_c)
+        assert np.all(same[far & hit_c]), f"{name} camera {k}: previous depth >= tFar changed a hit"
+        assert not np.any(touched[far & ~hit_c])
+        changed += int(touched.sum())
+    assert changed > 0
+
+
 @pytest.mark.parametrize("name,n_cams", (("cube", 60), ("stanford-bunny", 12), ("spot", 12), ("as1-oc-214", 12)))
 def test_device_source_on_cpu_vs_oracle_seeded_cameras_mesh_outside(name, n_cams):
     """Our own BVH8 (and the brute-force path for the cube) against the oracle's every-triangle loop from outside the

@@ -208,6 +208,19 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
                       float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
                       uint32_t *prim);
 
+/* The same call for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Identical
+ * arguments and results, but the device staging of the rays and their results lives in one fixed file-scope device array
+ * (2.8 MiB, held by every GPU that loads the library until the process exits) instead of six buffers allocated and freed
+ * per call: the call makes no cudaMalloc / cudaFree and no allocating library call.  n > RT_INTERSECT_STATIC_MAX_RAYS is
+ * rejected with RT_ERR_INVALID (split the batch, or use rt_intersect_host).  All calls on a GPU share the array, which keeps
+ * the last call's contents (the result area is cleared at the start of each call); calls that overlap on one GPU would
+ * race: the library serialises its own calls per process and returns only when the results are on the host. */
+#define RT_INTERSECT_STATIC_MAX_RAYS 65536
+int rt_intersect_host_static(const rt_scene *scene, const float *origins, const float *dirs, uint32_t n, float t_near,
+                             float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
+                             uint32_t *prim);
+
 /* ---- device buffers and cross-process sharing (multi-GPU: one process per GPU) ----------------------- */
 /* The reference has one framebuffer in one address space.  With one process per GPU the root rank owns the
  * framebuffer (rt_device_malloc on its GPU), exports it (CUDA IPC), and every other rank opens it and passes the

@@ -67,6 +67,7 @@ SIGNATURES = {
     "rt_render_host": (_i, [_vp, C.POINTER(RtFrame), _vp, _vp, _vp, C.POINTER(_f), C.POINTER(_f),
                             C.POINTER(RtCounters)]),
     "rt_intersect_host": (_i, [_vp, _vp, _vp, _u32, _f, _f, _i, _f, _vp, _vp, _vp, _vp]),
+    "rt_intersect_host_static": (_i, [_vp, _vp, _vp, _u32, _f, _f, _i, _f, _vp, _vp, _vp, _vp]),
     "rt_device_malloc": (_i, [C.c_uint64, _pp]),
     "rt_device_free": (_i, [_vp]),
     "rt_ipc_export": (_i, [_vp, C.c_char_p]),

@@ -1204,6 +1204,101 @@ int rt_intersect_host(const rt_scene *scene, const float *origins, const float *
 }  // extern "C"
 
 // =============================================================================================================
+// rt_intersect_host_static: rt_intersect_host for callers that must not allocate (no counterpart in the reference).
+// rt_intersect_host stages the rays and their results in six device buffers it
+// cudaMallocs and frees on every call; here the same staging lives in ONE file-scope device array of fixed size, so the
+// call makes no cudaMalloc / cudaFree (nor any allocating library routine).  Every GPU that loads the library holds the
+// array (2.8 MiB) until the process exits.  All calls on a device share it and it keeps the last call's contents: the
+// result area of the n rays is cleared first, and calls that overlap on one GPU would race (inside one process they are
+// serialised by a mutex and the call is synchronous; nothing protects against a caller's own concurrent kernels on it).
+// =============================================================================================================
+namespace {
+constexpr size_t kStaticRays = RT_INTERSECT_STATIC_MAX_RAYS;
+// per ray: origin 12 B, direction 12 B, t 4 B, normal 12 B, prim 4 B, hit 1 B; each section starts 256-byte aligned
+// (kStaticRays is a multiple of 256)
+constexpr size_t kOffO = 0, kOffD = kOffO + kStaticRays * 12, kOffT = kOffD + kStaticRays * 12,
+                 kOffN = kOffT + kStaticRays * 4, kOffP = kOffN + kStaticRays * 12, kOffH = kOffP + kStaticRays * 4,
+                 kStaticBytes = kOffH + kStaticRays;
+static_assert(kStaticRays % 256 == 0, "sections of the static scratch must stay 256-byte aligned");
+}  // namespace
+// (in host code this name is a host-side stand-in, not a device address: cudaGetSymbolAddress below)
+static __device__ __align__(256) unsigned char g_ray_scratch[kStaticBytes];
+
+// clears the result area of the first n rays (device code names the array directly)
+static __global__ void ray_scratch_clear_kernel(uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  reinterpret_cast<float *>(g_ray_scratch + kOffT)[i] = 0.0f;
+  float *nrm = reinterpret_cast<float *>(g_ray_scratch + kOffN);
+  nrm[3 * i] = nrm[3 * i + 1] = nrm[3 * i + 2] = 0.0f;
+  reinterpret_cast<uint32_t *>(g_ray_scratch + kOffP)[i] = 0u;
+  g_ray_scratch[kOffH + i] = 0;
+}
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_ray_scratch_mu;
+unsigned char *g_ray_scratch_addr[kMaxDevices] = {};  // per device: the array's DEVICE address, resolved once
+
+// set-up, once per device, with that device current
+int ray_scratch_on(int device, unsigned char **out) {
+  if (device < 0 || device >= kMaxDevices) return fail(RT_ERR_INVALID, "device index out of range for the static scratch");
+  if (!g_ray_scratch_addr[device]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_ray_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_ray_scratch)");
+    if (!p) return fail(RT_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_ray_scratch_addr[device] = static_cast<unsigned char *>(p);
+  }
+  *out = g_ray_scratch_addr[device];
+  return RT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int rt_intersect_host_static(const rt_scene *scene, const float *origins, const float *dirs, uint32_t n, float t_near,
+                             float t_far, int has_plane, float plane_y, uint8_t *hit, float *t, float *normal,
+                             uint32_t *prim) {
+  if (!scene) return fail(RT_ERR_INVALID, "scene is null");
+  if (n > kStaticRays)
+    return fail(RT_ERR_INVALID, "rt_intersect_host_static: n = " + std::to_string(n) + " rays exceeds the static scratch (at most " +
+                                    std::to_string(kStaticRays) + " per call; split the batch or use rt_intersect_host)");
+  if (n == 0) return RT_OK;
+  if (!origins || !dirs) return fail(RT_ERR_INVALID, "origins / dirs must not be null");
+  const Replica &r0 = *scene->reps[0];
+  DeviceGuard g(r0.device);
+  if (!g.ok) return fail(RT_ERR_CUDA, "cannot select the scene's device");
+  std::lock_guard<std::mutex> lock(g_ray_scratch_mu);
+  unsigned char *base = nullptr;
+  int rc = ray_scratch_on(r0.device, &base);
+  if (rc) return rc;
+  float *dO = reinterpret_cast<float *>(base + kOffO), *dD = reinterpret_cast<float *>(base + kOffD);
+  float *dT = reinterpret_cast<float *>(base + kOffT), *dN = reinterpret_cast<float *>(base + kOffN);
+  uint32_t *dP = reinterpret_cast<uint32_t *>(base + kOffP);
+  uint8_t *dH = base + kOffH;
+  RT_CUDA(cudaMemcpy(dO, origins, (size_t)n * 12, cudaMemcpyHostToDevice));
+  RT_CUDA(cudaMemcpy(dD, dirs, (size_t)n * 12, cudaMemcpyHostToDevice));
+  ray_scratch_clear_kernel<<<(n + 255u) / 256u, 256>>>(n);  // the array keeps the last call's results
+  RT_CUDA(cudaGetLastError());
+  RayArgs a;
+  a.scene = r0.dev;
+  a.origins = dO; a.dirs = dD; a.n = n;
+  a.t_near = t_near; a.t_far = t_far;
+  a.has_plane = has_plane != 0; a.plane_y = plane_y;
+  a.hit = dH; a.t = dT; a.normal = dN; a.prim = dP;
+  RT_CUDA((g_math.load() == RT_MATH_FAST) ? fast::launch_rays(a, nullptr) : exact::launch_rays(a, nullptr));
+  RT_CUDA(cudaDeviceSynchronize());
+  if (hit) RT_CUDA(cudaMemcpy(hit, dH, (size_t)n, cudaMemcpyDeviceToHost));
+  if (t) RT_CUDA(cudaMemcpy(t, dT, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  if (normal) RT_CUDA(cudaMemcpy(normal, dN, (size_t)n * 12, cudaMemcpyDeviceToHost));
+  if (prim) RT_CUDA(cudaMemcpy(prim, dP, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return RT_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================================
 // device buffers + CUDA IPC (one process per GPU; tiles are stored into the root's framebuffer over NVLink)
 // =============================================================================================================
 extern "C" {

@@ -829,6 +829,9 @@ __device__ __forceinline__ bool oct_walk_leaf(const OctWalk &s, const OctreeDev 
 // Trees imported from the reference (rt_scene_create_mesh_bvh8) keep the literal slab test + sort8 network so
 // that their visit order, and with it every tie, is the reference's own.
 
+#ifndef RT_BVH_DEFER
+#define RT_BVH_DEFER 1  // fast path: push (node, lane), fetch the child word at pop time (else fetch all at push time)
+#endif
 template <bool COUNT>
 __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float tNear, float tFar, Counters &cnt) {
   Hit r = hit_none();
@@ -876,11 +879,17 @@ __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float
         key_cswap(key[1], key[4]); key_cswap(key[3], key[6]);
         key_cswap(key[2], key[4]); key_cswap(key[3], key[5]);
         key_cswap(key[3], key[4]);
+#if !RT_BVH_DEFER
         const uint32_t *childWord = reinterpret_cast<const uint32_t *>(n4 + 12);
+#endif
 #pragma unroll
         for (int i = 7; i >= 0; --i) {
           if (key[i] != 0xFFFFFFFFu) {  // far-to-near pushes: the nearest child pops first
+#if RT_BVH_DEFER
+            stackRef[sp] = (ref << 3) | (key[i] & 7u);  // (node, lane): the child word is fetched when the entry pops
+#else
             stackRef[sp] = __ldg(childWord + (key[i] & 7u));
+#endif
             stackT[sp] = __uint_as_float(key[i] & ~7u);
             ++sp;
           }
@@ -942,6 +951,9 @@ __device__ __forceinline__ Hit bvh_intersect(const MeshDev &m, V3 o, V3 d, float
       ref = stackRef[sp];
       if (!(r.hitten && r.t < stackT[sp])) break;
     }
+#if RT_BVH_DEFER
+    if (fastNode) ref = __ldg(reinterpret_cast<const uint32_t *>(reinterpret_cast<const float4 *>(m.nodes + (ref >> 3)) + 12) + (ref & 7u));
+#endif
   }
 done:
   if (r.hitten) {
